@@ -1,0 +1,101 @@
+/*
+ * include/rg.h -- C ABI of the B200 seeded region-growing engine (libb200rg.so).
+ *
+ * Plain C: pointers, sizes, ints.  No torch / C++ types.  Every entry point cites the
+ * reference interface it replaces (paths relative to the reference repository
+ * anonyomous4/parallel-c-programs).  Semantics frozen from the reference:
+ *   region = union of the connected components, under "grid neighbours with
+ *   abs((int)a-(int)b) < threshold", that contain a seed;  4-connectivity when nz == 1
+ *   (region.c:506), 6-connectivity otherwise (raycast.cu:290-292);  x fastest, then y, then z
+ *   (raycast.cu:178-180);  seeds are (x,y,z) triples, out-of-range seeds are ignored
+ *   (region.c:485), duplicates are harmless;  mask bytes are exactly 0 or 1.
+ *
+ * There is no CPU fallback: every call fails with RG_ERR_CUDA when no CUDA device is usable.
+ */
+#ifndef B200RG_RG_H
+#define B200RG_RG_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    RG_OK = 0,
+    RG_ERR_ARG = -1,        /* NULL pointer, non-positive size, nseeds < 0 ... */
+    RG_ERR_CUDA = -2,       /* CUDA runtime error (rg_last_error() has the text) */
+    RG_ERR_NOMEM = -3,      /* host or device allocation failed */
+    RG_ERR_INTERNAL = -4,   /* engine self-check failed (status word non-zero) */
+    RG_ERR_TOO_LARGE = -5   /* volume exceeds what this entry point supports */
+};
+
+typedef struct rg_ctx rg_ctx;
+
+/* ---- reference-shaped entry points -------------------------------------------------------- */
+
+/* replaces grow_region_gpu()        5-cuda-region-growing/raycast.cu:702-756
+ *          grow_region_gpu_shared() 5-cuda-region-growing/raycast.cu:759-822  (what main() runs, :833)
+ *          grow_region_serial()     5-cuda-region-growing/raycast.cu:281-318  (same mask, computed on the GPU)
+ * and the OpenCL twin grow_region_gpu() 6-opencl-region-growing/raycast.c:308-377.
+ * data = host 512^3 uint8, x fastest.  Seed (50,300,300), threshold 1, 6-connectivity
+ * (raycast.cu:275,286,775).  Returns a calloc-compatible 512^3 mask the caller free()s
+ * (raycast.cu:852), NULL on failure.  Unlike the reference kernels the mask never contains 2s. */
+unsigned char *grow_region_gpu(unsigned char *data);
+unsigned char *grow_region_gpu_shared(unsigned char *data);
+unsigned char *grow_region_serial(unsigned char *data);
+
+/* replaces the grow_region() + write_image() pair of 2-mpi-region-growing/region.c:493-533,572-580
+ * for one whole image: seeds = the four corner seeds of add_seeds() (region.c:450-490) expressed
+ * in global 0-based pixels (4,4),(w-6,4),(w-6,h-6),(4,h-6); threshold 2 (region.c:81).
+ * mask_out (w*h, may be NULL) receives the region; if apply != 0, image[i] *= (mask[i]==0) is
+ * applied in place on the device before the copy back (region.c:576). */
+int rg_grow_region_2d(unsigned char *image, int width, int height, unsigned char *mask_out, int apply);
+
+/* ---- parametrised entry points ------------------------------------------------------------- */
+
+/* Host buffers in, host mask out (H2D + grow + D2H on device 0 / the current device).
+ * Generalises the three growers above to any size, seed list and threshold. */
+int rg_grow(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
+            const int32_t *seeds_xyz, int nseeds, int threshold, uint8_t *mask_out);
+
+/* Context = per-device workspace (scratch for tile records, face lists, coarse union-find). */
+int rg_ctx_create(int device, rg_ctx **out);
+void rg_ctx_destroy(rg_ctx *ctx);
+
+/* Bytes of device scratch a grow of this size needs (worst case, so no call can overflow). */
+int64_t rg_workspace_bytes(int64_t nx, int64_t ny, int64_t nz, int nseeds);
+
+/* Pre-size the context's scratch so that later calls do not allocate. */
+int rg_ctx_reserve(rg_ctx *ctx, int64_t nx, int64_t ny, int64_t nz, int nseeds);
+
+/* Device-resident grow: d_image, d_seeds_xyz and d_mask are DEVICE pointers on the context's
+ * device; everything is enqueued on `stream` (a cudaStream_t, NULL = default stream) and the
+ * call returns without synchronising.  This is the timed region of bench.py ("value").
+ * The device analogue of the do{kernel}while(flag) loops at raycast.cu:737-745,804-811 -- with
+ * no host round trip: convergence is structural (one union-find pass), not iterative. */
+int rg_grow_device(rg_ctx *ctx, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+                   const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream);
+
+/* Synchronises the stream last used and returns RG_OK or RG_ERR_INTERNAL / RG_ERR_CUDA;
+ * stats (may be NULL) receives {nodes, status bits, mismatching faces, 0}. */
+int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);
+
+/* replaces write_image()'s loop, region.c:575-577, on the device: image[i] *= (mask[i] == 0). */
+int rg_apply_mask_device(rg_ctx *ctx, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream);
+
+const char *rg_last_error(void);
+
+/* ---- synthetic inputs on the device (replaces func()/create_data(), raycast.cu:114-158) ---- */
+/* kind: 1 = exercise geometry with hash noise (C1h), 2 = C2 image (n x n), 3 = C3 serpentine,
+ * 4 = C4 (exercise geometry + z-serpentine).  Cube / square of side n; seed = noise seed. */
+int rg_synth_device(int kind, uint8_t *d_out, int64_t n, uint64_t seed, void *stream);
+/* z-slab version: writes planes [z_begin, z_end) of the n^3 volume to d_out (slab-local). */
+int rg_synth_slab_device(int kind, uint8_t *d_out, int64_t n, int64_t z_begin, int64_t z_end, uint64_t seed, void *stream);
+/* seed lists that go with the synthetic inputs; out = max_seeds*(x,y,z) host ints; returns count */
+int rg_synth_seeds(int kind, int64_t n, uint64_t seed, int32_t *out_xyz, int max_seeds);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

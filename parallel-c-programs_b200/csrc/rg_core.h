@@ -1,0 +1,594 @@
+/*
+ * rg_core.h -- kernel bodies of the B200 seeded region-growing engine.
+ *
+ * Replaces the grow loops of the reference (citations relative to /root/reference):
+ *   2-mpi-region-growing/region.c:493-533   grow_region()          (2-D, 4-conn, |d| < T)
+ *   5-cuda-region-growing/raycast.cu:281-318 grow_region_serial()  (3-D, 6-conn)
+ *   5-cuda-region-growing/raycast.cu:534-574, 589-699, 702-822     the two CUDA growers
+ * It is NOT a translation of those.  The reference result equals "the union of the connected
+ * components of the graph {grid neighbours with |delta| < T} that contain a seed" (SURVEY.md
+ * section 0), so the engine labels components instead of sweeping a frontier:
+ *
+ *   pass A  (tile_pass_a)   one CTA per tile: stage the uint8 tile + 1-voxel halo in shared
+ *           memory, build x/y/z "similar" bit planes with byte-SIMD, run-based union-find on
+ *           16-bit parents in shared memory, give dense ids ("nodes") only to components that
+ *           own a cross-tile edge or a seed, emit per-face lists of node ids.  Reads 1 B/voxel.
+ *   pass B  (merge_faces)   union-find over the coarse node graph with lock-free hooking; seeds
+ *           are pre-hooked to node 0, so "in the region" == "root is node 0".  One launch, no
+ *           global iteration and no host round trip, whatever the region's diameter.
+ *   pass C  (tile_pass_c)   tiles with no selected node are zero-filled without reading the
+ *           image; the others recompute their local components and write 0/1 mask bytes with
+ *           16-byte stores.  Writes 1 B/voxel, reads <= 1 B/voxel.
+ *
+ * Every body is written against an `Exec` (thread id, parallel-for, barrier, scan) so that the
+ * same source runs as a CUDA block (rg_kernels.cu) and, for the CPU logic tests only, as a
+ * sequential loop (tests/emu).  See rg_port.h.
+ */
+#pragma once
+#include "rg_port.h"
+
+namespace rg {
+
+enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
+enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_MAXNODES = 3, CTR_WORDS = 8 };
+enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
+
+template <int TX_, int TY_, int TZ_>
+struct TileCfg {
+    static constexpr int TX = TX_, TY = TY_, TZ = TZ_;
+    static constexpr int WX = TX / 32;             /* 32-voxel words per row */
+    static constexpr int NW = WX * TY * TZ;        /* words per tile */
+    static constexpr int NV = TX * TY * TZ;        /* voxels per tile */
+    static constexpr int HZ = TZ > 1 ? 1 : 0;      /* z halo planes (none for images) */
+    static constexpr int PZ = TZ + 2 * HZ, PY = TY + 2;
+    static constexpr int CX = TX / 16;             /* 16-byte chunks per row */
+    static constexpr int FXN = TY * TZ, FYN = TX * TZ, FZN = HZ ? TX * TY : 0;
+    static constexpr int FXW = (FXN + 31) / 32, FYW = WX * TZ, FZW = HZ ? WX * TY : 0;
+    static constexpr int FW_TOTAL = 2 * (FXW + FYW + FZW);
+    static constexpr int ENT_MAX = 2 * (FXN + FYN + FZN);   /* face-list entries per tile, worst case */
+    static_assert(TX % 32 == 0, "rows are whole words");
+    static_assert(NV <= 65536, "16-bit tile-local indices");
+    RG_MFN static constexpr int fw_off(int f)
+    {
+        return f == 0 ? 0 : f == 1 ? FXW : f == 2 ? 2 * FXW : f == 3 ? 2 * FXW + FYW
+             : f == 4 ? 2 * FXW + 2 * FYW : f == 5 ? 2 * FXW + 2 * FYW + FZW : FW_TOTAL;
+    }
+};
+
+/* tile shapes: 32768 voxels either way */
+typedef TileCfg<64, 32, 16> Cfg3D;
+typedef TileCfg<128, 256, 1> Cfg2D;
+
+struct TileRec {                 /* 32 bytes per tile, written by pass A */
+    uint32_t node_base;          /* first global node id of this tile */
+    uint32_t nnodes;
+    uint16_t cnt[6];             /* face-list lengths, order XM XP YM YP ZM ZP */
+    uint16_t pad0, pad1;
+    uint32_t pad2, pad3;
+};
+
+struct Params {
+    const uint8_t *image;        /* plane z = 0 of this slab; planes -1 / nz readable if z*_ext */
+    uint8_t *mask;
+    int64_t nx, ny, nz;
+    int32_t ntx, nty, ntz;
+    int32_t zlo_ext, zhi_ext;    /* slab has a neighbour slab below / above (multi-GPU) */
+    int32_t tmode;               /* 0: T <= 0 (no edges)  1: 1..255  2: T >= 256 (all edges) */
+    uint32_t t4;                 /* T replicated into 4 bytes */
+    int32_t fast16;              /* nx % 16 == 0 and both buffers 16-byte aligned */
+    const uint64_t *seed_keys;   /* sorted (tile << 16 | voxel-in-tile); ~0 = dropped */
+    int32_t nseeds;
+    TileRec *rec;
+    uint16_t *ent;               /* [ntiles][ENT_MAX] node ids local to the tile */
+    uint32_t *nparent;           /* coarse union-find; node 0 = "holds a seed" */
+    uint16_t *nrep;              /* node -> root voxel index inside its tile */
+    uint32_t *counters;          /* CTR_* */
+    uint32_t node_cap;
+};
+
+/* ---------------------------------------------------------------- shared-memory tile state */
+template <class C>
+struct alignas(16) TileSmem {
+    union alignas(16) U {
+        struct {
+            uint8_t img[C::PZ * C::PY * C::TX];    /* tile + y/z halo rows */
+            uint8_t xm[C::TY * C::TZ];             /* x = -1 column */
+            uint8_t xp[C::TY * C::TZ];             /* x = TX column */
+        } i;
+        uint16_t parent[C::NV];                    /* run union-find (image is dead by then) */
+    } u;
+    uint32_t ex[C::NW], ey[C::NW], ez[C::NW];      /* bit i: voxel i similar to its +x/+y/+z neighbour (in-tile) */
+    uint32_t fmask[C::FW_TOTAL];                   /* cross-tile edges per face, de-duplicated */
+    uint16_t fprefix[C::FW_TOTAL + 2];
+    uint16_t ent_root[C::ENT_MAX];
+    uint32_t openbits[C::NW], seedbits[C::NW];
+    uint16_t wprefix[C::NW];
+    uint32_t scal[16];
+    uint32_t scan_scratch[40];
+};
+enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6 };
+
+/* ---------------------------------------------------------------- small helpers */
+RG_FN uint32_t valid_bits(int64_t n) { return n >= 32 ? 0xFFFFFFFFu : n <= 0 ? 0u : ((1u << n) - 1u); }
+
+RG_FN void load8(const uint8_t *p, uint32_t a[8])
+{
+    u32x4 lo = ld128(p), hi = ld128(p + 16);
+    a[0] = lo.x; a[1] = lo.y; a[2] = lo.z; a[3] = lo.w; a[4] = hi.x; a[5] = hi.y; a[6] = hi.z; a[7] = hi.w;
+}
+RG_FN void shift8(const uint32_t a[8], uint32_t next_byte, uint32_t b[8])
+{
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+    for (int j = 0; j < 7; j++) b[j] = (a[j] >> 8) | (a[j + 1] << 24);
+    b[7] = (a[7] >> 8) | (next_byte << 24);
+}
+RG_FN uint32_t edge_word(const uint32_t a[8], const uint32_t b[8], int tmode, uint32_t t4)
+{
+    if (tmode == 0) return 0u;
+    if (tmode == 2) return 0xFFFFFFFFu;
+    uint32_t w = 0;
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+    for (int j = 0; j < 8; j++) w |= edge4(a[j], b[j], t4) << (4 * j);
+    return w;
+}
+RG_FN bool similar1(uint32_t a, uint32_t b, int tmode, uint32_t t4)
+{
+    if (tmode == 0) return false;
+    if (tmode == 2) return true;
+    int d = (int)a - (int)b; if (d < 0) d = -d;
+    return d < (int)(t4 & 0xFF);
+}
+/* x-edges inside one 32-voxel word (bit 31 is meaningless) */
+RG_FN uint32_t xedges_within(const uint32_t a[8], int tmode, uint32_t t4)
+{
+    uint32_t b[8]; shift8(a, 0, b);
+    return edge_word(a, b, tmode, t4);
+}
+/* keep one cross edge per pair of overlapping x-runs: bit i is redundant if bit i-1 is a cross
+   edge too and both rows continue from i-1 to i.  Both sides of a face evaluate this on the
+   same voxel values, so their lists stay aligned entry by entry. */
+RG_FN uint32_t dedupe(uint32_t m, uint32_t ex_a, uint32_t ex_b) { return m & ~((m & ex_a & ex_b) << 1); }
+
+RG_FN uint32_t run_start(uint32_t exw, int w, int bit)
+{
+    uint32_t S = ~(exw << 1);                                   /* bit 0 always starts a run */
+    return (uint32_t)(w * 32 + 31 - clz(S & (0xFFFFFFFFu >> (31 - bit))));
+}
+
+/* lock-free union-find, roots are minima (after ECL-CC, Jaiganesh & Burtscher 2018) */
+RG_FN uint32_t find16(uint16_t *par, uint32_t x)
+{
+    uint32_t curr = ldv16(par + x);
+    if (curr != x) {
+        uint32_t prev = x, next;
+        while (curr > (next = ldv16(par + curr))) { stv16(par + prev, (uint16_t)next); prev = curr; curr = next; }
+    }
+    return curr;
+}
+RG_FN void unite16(uint16_t *par, uint32_t a, uint32_t b)
+{
+    a = find16(par, a); b = find16(par, b);
+    while (a != b) {
+        if (a < b) { uint32_t t = a; a = b; b = t; }
+        uint32_t old = cas16(par + a, (uint16_t)a, (uint16_t)b);
+        if (old == a) break;
+        a = old;
+    }
+}
+RG_FN uint32_t find32(uint32_t *par, uint32_t x)
+{
+    uint32_t curr = ldv32(par + x);
+    if (curr != x) {
+        uint32_t prev = x, next;
+        while (curr > (next = ldv32(par + curr))) { stv32(par + prev, next); prev = curr; curr = next; }
+    }
+    return curr;
+}
+RG_FN void unite32(uint32_t *par, uint32_t a, uint32_t b)
+{
+    a = find32(par, a); b = find32(par, b);
+    while (a != b) {
+        if (a < b) { uint32_t t = a; a = b; b = t; }
+        uint32_t old = cas32(par + a, a, b);
+        if (old == a) break;
+        a = old;
+    }
+}
+
+template <class C>
+RG_FN void tile_origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz)
+{
+    tx = (int)(tile % (uint32_t)P.ntx);
+    uint32_t r = tile / (uint32_t)P.ntx;
+    ty = (int)(r % (uint32_t)P.nty);
+    tz = (int)(r / (uint32_t)P.nty);
+}
+
+template <class C> RG_FN int img_off(int x, int y, int z) { return ((z + C::HZ) * C::PY + (y + 1)) * C::TX + x; }
+
+/* ---------------------------------------------------------------- stage a tile in shared memory */
+template <class C, class Exec>
+RG_FN void load_tile(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, int64_t y0, int64_t z0, bool halo)
+{
+    const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
+    const int64_t zmin = -(int64_t)P.zlo_ext, zmax = nz + P.zhi_ext;          /* readable plane range */
+    ex.pfor(C::PZ * C::PY * C::CX, [&](int it) {
+        int c = it % C::CX, r = it / C::CX;
+        int py = r % C::PY, pz = r / C::PY;
+        int ly = py - 1, lz = pz - C::HZ;
+        bool yh = (ly < 0 || ly >= C::TY), zh = (lz < 0 || lz >= C::TZ);
+        int64_t gx = x0 + 16 * c, gy = y0 + ly, gz = z0 + lz;
+        u32x4 v = {0, 0, 0, 0};
+        bool want = !(yh && zh) && (halo || !(yh || zh));
+        if (want && gy >= 0 && gy < ny && gz >= zmin && gz < zmax && gx < nx) {
+            const uint8_t *g = P.image + (gz * ny + gy) * nx + gx;
+            if (P.fast16) v = ld128_stream(g);
+            else {
+                uint32_t t[4] = {0, 0, 0, 0};
+                for (int b = 0; b < 16; b++) if (gx + b < nx) t[b >> 2] |= (uint32_t)g[b] << (8 * (b & 3));
+                v = u32x4{t[0], t[1], t[2], t[3]};
+            }
+        }
+        st128(&s.u.i.img[(pz * C::PY + py) * C::TX + 16 * c], v);
+    });
+    if (halo) {
+        ex.pfor(2 * C::TY * C::TZ, [&](int it) {
+            int side = it / (C::TY * C::TZ), q = it % (C::TY * C::TZ);
+            int ly = q % C::TY, lz = q / C::TY;
+            int64_t gy = y0 + ly, gz = z0 + lz, gx = side ? x0 + C::TX : x0 - 1;
+            uint8_t v = 0;
+            if (gy < ny && gz < nz && gx >= 0 && gx < nx) v = P.image[(gz * ny + gy) * nx + gx];
+            (side ? s.u.i.xp : s.u.i.xm)[q] = v;
+        });
+    }
+}
+
+/* ---------------------------------------------------------------- edge bit planes (+ face masks if FACES) */
+template <class C, bool FACES, class Exec>
+RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, int64_t y0, int64_t z0)
+{
+    const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
+    const int tmode = P.tmode; const uint32_t t4 = P.t4;
+    const int vy = (int)((ny - y0) < C::TY ? (ny - y0) : C::TY);
+    const int vz = (int)((nz - z0) < C::TZ ? (nz - z0) : C::TZ);
+    const bool has_yp = y0 + C::TY < ny, has_ym = y0 > 0;
+    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && P.zhi_ext));
+    const bool has_zm = C::HZ && (z0 > 0 || P.zlo_ext);
+    ex.pfor(C::NW, [&](int w) {
+        int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+        int64_t gx0 = x0 + 32 * wx;
+        uint32_t vmask = (y < vy && z < vz) ? valid_bits(nx - gx0) : 0u;
+        uint32_t exw = 0, eyw = 0, ezw = 0;
+        if (vmask) {
+            const uint8_t *rowp = &s.u.i.img[img_off<C>(32 * wx, y, z)];
+            uint32_t a[8], b[8];
+            load8(rowp, a);
+            /* +x */
+            uint32_t nextb = 0;
+            if (wx < C::WX - 1) nextb = rowp[32];
+            else if (FACES) nextb = s.u.i.xp[z * C::TY + y];
+            shift8(a, nextb, b);
+            uint32_t nextvalid = (gx0 + 32 < nx) ? 0x80000000u : 0u;
+            uint32_t e = edge_word(a, b, tmode, t4) & vmask & ((vmask >> 1) | nextvalid);
+            if (wx == C::WX - 1) {
+                if (FACES && (e >> 31)) { int bi = z * C::TY + y; atomic_or(&s.fmask[C::fw_off(F_XP) + (bi >> 5)], 1u << (bi & 31)); }
+                e &= 0x7FFFFFFFu;
+            }
+            exw = e;
+            if (FACES && wx == 0 && x0 > 0 && (vmask & 1u)) {
+                if (similar1(s.u.i.xm[z * C::TY + y], a[0] & 0xFFu, tmode, t4)) {
+                    int bi = z * C::TY + y; atomic_or(&s.fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31));
+                }
+            }
+            /* +y */
+            if (y < vy - 1) {
+                load8(rowp + C::TX, b);
+                eyw = edge_word(a, b, tmode, t4) & vmask;
+            } else if (FACES && has_yp) {                       /* y == TY-1: edges into the +y tile */
+                load8(rowp + C::TX, b);
+                uint32_t m = edge_word(a, b, tmode, t4) & vmask;
+                s.fmask[C::fw_off(F_YP) + z * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
+            }
+            if (FACES && y == 0 && has_ym) {
+                load8(rowp - C::TX, b);
+                uint32_t m = edge_word(b, a, tmode, t4) & vmask;
+                s.fmask[C::fw_off(F_YM) + z * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
+            }
+            /* +z */
+            if (C::HZ) {
+                const int zs = C::PY * C::TX;
+                if (z < vz - 1) {
+                    load8(rowp + zs, b);
+                    ezw = edge_word(a, b, tmode, t4) & vmask;
+                } else if (FACES && has_zp) {                   /* top valid plane: edges into the +z tile / slab */
+                    load8(rowp + zs, b);
+                    uint32_t m = edge_word(a, b, tmode, t4) & vmask;
+                    s.fmask[C::fw_off(F_ZP) + y * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
+                }
+                if (FACES && z == 0 && has_zm) {
+                    load8(rowp - zs, b);
+                    uint32_t m = edge_word(b, a, tmode, t4) & vmask;
+                    s.fmask[C::fw_off(F_ZM) + y * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
+                }
+            }
+        }
+        s.ex[w] = exw; s.ey[w] = eyw; s.ez[w] = ezw;
+    });
+}
+
+/* ---------------------------------------------------------------- run-based union-find inside the tile */
+template <class C, class Exec>
+RG_FN void label_runs(Exec &ex, TileSmem<C> &s)
+{
+    /* parent[v] = v, eight 16-bit entries per 16-byte store */
+    ex.pfor(C::NV / 8, [&](int it) {
+        uint32_t v = (uint32_t)it * 8;
+        u32x4 q = { v | ((v + 1) << 16), (v + 2) | ((v + 3) << 16), (v + 4) | ((v + 5) << 16), (v + 6) | ((v + 7) << 16) };
+        st128(&s.u.parent[v], q);
+    });
+    ex.sync();
+    ex.pfor(C::NW, [&](int w) {
+        int wx = w % C::WX;
+        uint32_t exw = s.ex[w];
+        if (wx > 0) {
+            uint32_t exl = s.ex[w - 1];
+            if (exl >> 31) unite16(s.u.parent, run_start(exl, w - 1, 31), (uint32_t)w * 32);
+        }
+        uint32_t m = s.ey[w];
+        if (m) {
+            int up = w + C::WX; uint32_t exu = s.ex[up];
+            uint32_t n = dedupe(m, exw, exu);
+            while (n) { int i = ffs1(n) - 1; n &= n - 1; unite16(s.u.parent, run_start(exw, w, i), run_start(exu, up, i)); }
+        }
+        m = s.ez[w];
+        if (m) {
+            int up = w + C::WX * C::TY; uint32_t exu = s.ex[up];
+            uint32_t n = dedupe(m, exw, exu);
+            while (n) { int i = ffs1(n) - 1; n &= n - 1; unite16(s.u.parent, run_start(exw, w, i), run_start(exu, up, i)); }
+        }
+    });
+    ex.sync();
+}
+
+/* ================================================================ pass A */
+template <class C, class Exec>
+RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
+{
+    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
+    const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
+
+    ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
+    ex.pfor(C::NW, [&](int i) { s.openbits[i] = 0; s.seedbits[i] = 0; });
+    if (ex.tid() == 0) {
+        /* this tile's slice of the sorted seed keys */
+        uint64_t lo_key = (uint64_t)tile << 16, hi_key = ((uint64_t)tile + 1) << 16;
+        int lo = 0, hi = P.nseeds;
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < lo_key) lo = mid + 1; else hi = mid; }
+        int a = lo; hi = P.nseeds;
+        while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
+        s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0;
+    }
+    load_tile<C>(ex, P, s, x0, y0, z0, true);
+    ex.sync();
+    build_edges<C, true>(ex, P, s, x0, y0, z0);
+    ex.sync();
+    label_runs<C>(ex, s);
+
+    /* positions of the face-list entries */
+    uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
+    if (ex.tid() == 0) { s.fprefix[C::FW_TOTAL] = (uint16_t)etot; s.scal[SC_ETOT] = etot; }
+    ex.sync();
+
+    /* roots of every component that owns a cross-tile edge ... */
+    ex.pfor(C::FW_TOTAL, [&](int fw) {
+        uint32_t m = s.fmask[fw];
+        if (!m) return;
+        int f = 0; while (fw >= C::fw_off(f + 1)) f++;
+        int idx = fw - C::fw_off(f);
+        uint32_t slot = s.fprefix[fw];
+        while (m) {
+            int b = ffs1(m) - 1; m &= m - 1;
+            int x, y, z;
+            if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
+            else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? C::TY - 1 : 0; }
+            else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
+            int w = (z * C::TY + y) * C::WX + (x >> 5);
+            uint32_t r = find16(s.u.parent, run_start(s.ex[w], w, x & 31));
+            atomic_or(&s.openbits[r >> 5], 1u << (r & 31));
+            s.ent_root[slot++] = (uint16_t)r;
+        }
+    });
+    /* ... or a seed */
+    {
+        int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
+        ex.pfor(hi - lo, [&](int i) {
+            uint32_t v = (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu);
+            int w = (int)(v >> 5);
+            uint32_t r = find16(s.u.parent, run_start(s.ex[w], w, (int)(v & 31)));
+            atomic_or(&s.openbits[r >> 5], 1u << (r & 31));
+            atomic_or(&s.seedbits[r >> 5], 1u << (r & 31));
+        });
+    }
+    ex.sync();
+
+    /* dense node ids in root order */
+    uint32_t k = ex.scan16(C::NW, [&](int i) { return (uint32_t)popc(s.openbits[i]); }, s.wprefix, s.scan_scratch);
+    if (ex.tid() == 0) {
+        uint32_t base = k ? atomic_add(&P.counters[CTR_NODES], k) : 0u;
+        if (k && (base + k > P.node_cap || base + k < base)) { atomic_or(&P.counters[CTR_STATUS], ST_NODE_OVERFLOW); s.scal[SC_OVERFLOW] = 1; }
+        s.scal[SC_NODE_BASE] = base; s.scal[SC_NNODES] = k;
+    }
+    ex.sync();
+    const uint32_t base = s.scal[SC_NODE_BASE];
+    const bool ok = !s.scal[SC_OVERFLOW];
+    if (ok) {
+        ex.pfor(C::NW, [&](int wi) {
+            uint32_t m = s.openbits[wi];
+            if (!m) return;
+            uint32_t id = s.wprefix[wi], sb = s.seedbits[wi];
+            while (m) {
+                int b = ffs1(m) - 1; m &= m - 1;
+                uint32_t g = base + id++;
+                P.nparent[g] = ((sb >> b) & 1u) ? 0u : g;       /* seeded components start hooked to node 0 */
+                P.nrep[g] = (uint16_t)(wi * 32 + b);
+            }
+        });
+        uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
+        ex.pfor((int)s.scal[SC_ETOT], [&](int e) {
+            uint32_t r = s.ent_root[e];
+            ent[e] = (uint16_t)(s.wprefix[r >> 5] + popc(s.openbits[r >> 5] & ((1u << (r & 31)) - 1u)));
+        });
+    }
+    if (ex.tid() == 0) {
+        TileRec rc;
+        rc.node_base = base; rc.nnodes = ok ? k : 0u;
+        for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]) : (uint16_t)0;
+        rc.pad0 = rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
+        P.rec[tile] = rc;
+    }
+}
+
+/* ================================================================ pass B: one (tile, +face) per item */
+template <class C, class Exec>
+RG_FN void merge_faces(Exec &ex, const Params &P)
+{
+    const uint32_t ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
+    ex.gpfor((int64_t)ntiles * 3, [&](int64_t it) {
+        uint32_t tile = (uint32_t)(it / 3); int axis = (int)(it % 3);
+        int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+        uint32_t nb;
+        if (axis == 0) { if (tx + 1 >= P.ntx) return; nb = tile + 1; }
+        else if (axis == 1) { if (ty + 1 >= P.nty) return; nb = tile + (uint32_t)P.ntx; }
+        else { if (tz + 1 >= P.ntz) return; nb = tile + (uint32_t)P.ntx * (uint32_t)P.nty; }
+        const TileRec &ra = P.rec[tile];
+        const int fa = 2 * axis + 1, fb = 2 * axis;
+        uint32_t cnt = ra.cnt[fa];
+        if (!cnt) return;
+        const TileRec &rb = P.rec[nb];
+        if (rb.cnt[fb] != cnt) { atomic_or(&P.counters[CTR_STATUS], ST_FACE_MISMATCH); atomic_add(&P.counters[CTR_FACE_MISMATCH], 1u); return; }
+        uint32_t offa = 0, offb = 0;
+        for (int f = 0; f < fa; f++) offa += ra.cnt[f];
+        for (int f = 0; f < fb; f++) offb += rb.cnt[f];
+        const uint16_t *ea = P.ent + (size_t)tile * C::ENT_MAX + offa;
+        const uint16_t *eb = P.ent + (size_t)nb * C::ENT_MAX + offb;
+        uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu;
+        for (uint32_t i = 0; i < cnt; i++) {
+            uint32_t a = ra.node_base + ea[i], b = rb.node_base + eb[i];
+            if (a == pa && b == pb) continue;
+            unite32(P.nparent, a, b);
+            pa = a; pb = b;
+        }
+    });
+}
+
+/* ================================================================ pass C */
+template <class C, class Exec>
+RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0)
+{
+    ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+        int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+        int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
+        if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
+        uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
+        if (P.fast16) st128_stream(g, u32x4{0, 0, 0, 0});
+        else for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = 0;
+    });
+}
+
+template <class C, class Exec>
+RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
+{
+    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
+    const TileRec rc = P.rec[tile];
+    uint32_t *rootflag = s.openbits;                           /* bit r: tile-local root r is in the region */
+
+    if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    ex.pfor(C::NW, [&](int i) { rootflag[i] = 0; });
+    if (ex.tid() == 0) s.scal[SC_ANY] = 0;
+    ex.sync();
+    ex.pfor((int)rc.nnodes, [&](int i) {
+        uint32_t g = rc.node_base + (uint32_t)i;
+        if (find32(P.nparent, g) == 0u) {
+            uint32_t r = P.nrep[g];
+            atomic_or(&rootflag[r >> 5], 1u << (r & 31));
+            s.scal[SC_ANY] = 1;
+        }
+    });
+    ex.sync();
+    if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+
+    load_tile<C>(ex, P, s, x0, y0, z0, false);
+    ex.sync();
+    build_edges<C, false>(ex, P, s, x0, y0, z0);
+    ex.sync();
+    label_runs<C>(ex, s);
+
+    uint32_t *outw = s.seedbits;                               /* region bits per word */
+    ex.pfor(C::NW, [&](int w) {
+        int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+        uint32_t exw = s.ex[w];
+        /* voxels with at least one edge; the others are singletons whose only way in is to be a root */
+        uint32_t he = exw | (exw << 1) | s.ey[w] | s.ez[w];
+        if (wx > 0) he |= s.ex[w - 1] >> 31;
+        if (y > 0) he |= s.ey[w - C::WX];
+        if (z > 0) he |= s.ez[w - C::WX * C::TY];
+        uint32_t out = rootflag[w] & ~he;
+        uint32_t S = ~(exw << 1), rem = S;
+        while (rem) {
+            int i = ffs1(rem) - 1; rem &= rem - 1;
+            int j = rem ? ffs1(rem) - 1 : 32;                  /* run = bits [i, j) */
+            uint32_t rm = (j == 32 ? 0xFFFFFFFFu : ((1u << j) - 1u)) & ~((1u << i) - 1u);
+            if (!(rm & he)) continue;
+            uint32_t r = find16(s.u.parent, (uint32_t)w * 32 + i);
+            if ((rootflag[r >> 5] >> (r & 31)) & 1u) out |= rm;
+        }
+        outw[w] = out;
+    });
+    ex.sync();
+    ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+        int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+        int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
+        if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
+        uint32_t bits = (outw[(z * C::TY + y) * C::WX + (c >> 1)] >> ((c & 1) * 16)) & 0xFFFFu;
+        u32x4 v = { expand4(bits & 15u), expand4((bits >> 4) & 15u), expand4((bits >> 8) & 15u), expand4(bits >> 12) };
+        uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
+        if (P.fast16) st128_stream(g, v);
+        else {
+            uint32_t t[4] = { v.x, v.y, v.z, v.w };
+            for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = (uint8_t)((t[b >> 2] >> (8 * (b & 3))) & 0xFFu);
+        }
+    });
+}
+
+/* ================================================================ seeds -> sortable keys */
+template <class C, class Exec>
+RG_FN void make_seed_keys(Exec &ex, const Params &P, const int32_t *seeds_xyz, uint64_t *keys)
+{
+    ex.gpfor((int64_t)P.nseeds, [&](int64_t i) {
+        int64_t x = seeds_xyz[3 * i], y = seeds_xyz[3 * i + 1], z = seeds_xyz[3 * i + 2];
+        uint64_t key = ~0ull;                                   /* out of range: dropped (region.c:485) */
+        if (x >= 0 && x < P.nx && y >= 0 && y < P.ny && z >= 0 && z < P.nz) {
+            int64_t tx = x / C::TX, ty = y / C::TY, tz = z / C::TZ;
+            uint64_t tile = (uint64_t)((tz * P.nty + ty) * P.ntx + tx);
+            uint32_t v = (uint32_t)(((z - tz * C::TZ) * C::TY + (y - ty * C::TY)) * C::TX + (x - tx * C::TX));
+            key = (tile << 16) | v;
+        }
+        keys[i] = key;
+    });
+}
+
+/* resets the per-call counters; node 0 is the "holds a seed" super node */
+RG_FN void reset_counters(const Params &P)
+{
+    for (int i = 0; i < CTR_WORDS; i++) P.counters[i] = 0;
+    P.counters[CTR_NODES] = 1;
+    P.nparent[0] = 0;
+}
+
+} // namespace rg

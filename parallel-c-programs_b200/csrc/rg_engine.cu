@@ -1,0 +1,422 @@
+/*
+ * rg_engine.cu -- CUDA kernels (sm_100a) + context + C ABI of the region-growing engine.
+ *
+ * Kernel bodies live in rg_core.h (see the pass A / B / C description there); this file wraps
+ * them in __global__ functions, owns the per-device scratch ("context") and implements the
+ * entry points declared in include/rg.h.  There is deliberately no CPU path in this library.
+ */
+#include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <mutex>
+
+#include "rg_core.h"
+#include "../../include/rg.h"
+
+using namespace rg;
+
+/* ------------------------------------------------------------------ Exec for a CUDA block */
+struct DevExec {
+    __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
+    template <class F> __device__ __forceinline__ void pfor(int n, F f)
+    {
+        for (int i = (int)threadIdx.x; i < n; i += (int)blockDim.x) f(i);
+    }
+    template <class F> __device__ __forceinline__ void gpfor(int64_t n, F f)
+    {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) f(i);
+    }
+    __device__ __forceinline__ void sync() { __syncthreads(); }
+    /* block-wide exclusive scan of count(i), i < n, into out[i]; returns the total to every thread */
+    template <class F> __device__ __forceinline__ uint32_t scan16(int n, F count, uint16_t *out, uint32_t *scratch)
+    {
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+        uint32_t base = 0;
+        for (int start = 0; start < n; start += (int)blockDim.x) {
+            int i = start + (int)threadIdx.x;
+            uint32_t c = i < n ? count(i) : 0u, incl = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+            if (lane == 31) scratch[wid] = incl;
+            __syncthreads();
+            if (wid == 0) {
+                uint32_t v = lane < nwarp ? scratch[lane] : 0u, inc2 = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc2, d); if (lane >= d) inc2 += t; }
+                scratch[lane] = inc2 - v;
+                if (lane == 31) scratch[32] = inc2;
+            }
+            __syncthreads();
+            if (i < n) out[i] = (uint16_t)(base + scratch[wid] + incl - c);
+            base += scratch[32];
+            __syncthreads();
+        }
+        return base;
+    }
+};
+
+/* ------------------------------------------------------------------ kernels */
+#define RG_THREADS 512
+
+template <class C>
+__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a(const Params P)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DevExec ex;
+    tile_pass_a<C>(ex, P, blockIdx.x, *reinterpret_cast<TileSmem<C> *>(smem_raw));
+}
+
+template <class C>
+__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DevExec ex;
+    tile_pass_c<C>(ex, P, blockIdx.x, *reinterpret_cast<TileSmem<C> *>(smem_raw));
+}
+
+template <class C>
+__global__ void __launch_bounds__(256) k_merge(const Params P)
+{
+    DevExec ex;
+    merge_faces<C>(ex, P);
+}
+
+template <class C>
+__global__ void __launch_bounds__(256) k_seed_keys(const Params P, const int32_t *seeds_xyz, uint64_t *keys)
+{
+    DevExec ex;
+    if (blockIdx.x == 0 && threadIdx.x == 0) reset_counters(P);
+    make_seed_keys<C>(ex, P, seeds_xyz, keys);
+}
+
+/* bitonic sort of up to 2048 keys in one block (the usual case: a handful of seeds) */
+__global__ void __launch_bounds__(1024) k_sort_small(uint64_t *keys, int n)
+{
+    __shared__ uint64_t sk[2048];
+    for (int i = threadIdx.x; i < 2048; i += blockDim.x) sk[i] = i < n ? keys[i] : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= 2048; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < 2048; i += blockDim.x) {
+                int p = i ^ j;
+                if (p > i) {
+                    uint64_t a = sk[i], b = sk[p];
+                    bool up = (i & k) == 0;
+                    if ((a > b) == up) { sk[i] = b; sk[p] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) keys[i] = sk[i];
+}
+
+__global__ void __launch_bounds__(256) k_apply_mask(uint8_t *image, const uint8_t *mask, int64_t n)
+{
+    /* region.c:576  image[i] *= (region[i] == 0) */
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) if (mask[i]) image[i] = 0;
+}
+
+/* ------------------------------------------------------------------ errors */
+static thread_local char g_err[512] = "";
+static int fail(int code, const char *what, cudaError_t e = cudaSuccess)
+{
+    if (e != cudaSuccess) snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(g_err, sizeof g_err, "%s", what);
+    return code;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(RG_ERR_CUDA, #call, e_); } while (0)
+
+extern "C" const char *rg_last_error(void) { return g_err; }
+
+/* ------------------------------------------------------------------ context */
+struct rg_ctx {
+    int device;
+    void *ws; size_t ws_bytes;                 /* engine scratch */
+    uint8_t *d_image, *d_mask; size_t io_bytes; /* staging for the host-pointer entry points */
+    int32_t *d_seeds; size_t seeds_cap;
+    uint32_t *h_status;                        /* pinned, CTR_WORDS words */
+    uint32_t *last_counters;                   /* device counters of the last call */
+    cudaStream_t last_stream;
+    bool attr_set;
+};
+
+struct Layout {
+    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, total;
+    uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
+};
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+template <class C>
+static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L)
+{
+    int64_t ntx = (nx + C::TX - 1) / C::TX, nty = (ny + C::TY - 1) / C::TY, ntz = (nz + C::TZ - 1) / C::TZ;
+    int64_t ntiles = ntx * nty * ntz;
+    int64_t node_cap = 1 + ntiles * (int64_t)C::ENT_MAX + (int64_t)nseeds;
+    if (ntiles >= (1ll << 31) || node_cap >= (1ll << 32)) return fail(RG_ERR_TOO_LARGE, "volume too large for 32-bit node ids");
+    L.ntx = (int)ntx; L.nty = (int)nty; L.ntz = (int)ntz; L.ntiles = (uint32_t)ntiles; L.node_cap = (uint32_t)node_cap;
+    size_t o = 0;
+    L.off_rec = o;  o = align_up(o + (size_t)ntiles * sizeof(TileRec), 256);
+    L.off_ent = o;  o = align_up(o + (size_t)ntiles * C::ENT_MAX * sizeof(uint16_t), 256);
+    L.off_npar = o; o = align_up(o + (size_t)node_cap * sizeof(uint32_t), 256);
+    L.off_nrep = o; o = align_up(o + (size_t)node_cap * sizeof(uint16_t), 256);
+    L.off_ctr = o;  o = align_up(o + CTR_WORDS * sizeof(uint32_t), 256);
+    size_t nk = (size_t)(nseeds > 0 ? nseeds : 1);
+    L.off_keys = o;  o = align_up(o + nk * 8, 256);
+    L.off_keys2 = o; o = align_up(o + nk * 8, 256);
+    L.cub_bytes = 0;
+    if (nseeds > 2048) {
+        size_t tb = 0;
+        cub::DeviceRadixSort::SortKeys(nullptr, tb, (const uint64_t *)nullptr, (uint64_t *)nullptr, nseeds);
+        L.cub_bytes = tb;
+    }
+    L.off_cub = o; o = align_up(o + L.cub_bytes, 256);
+    L.total = o;
+    return RG_OK;
+}
+
+static int layout_for(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L)
+{
+    return nz == 1 ? make_layout<Cfg2D>(nx, ny, nz, nseeds, L) : make_layout<Cfg3D>(nx, ny, nz, nseeds, L);
+}
+
+extern "C" int64_t rg_workspace_bytes(int64_t nx, int64_t ny, int64_t nz, int nseeds)
+{
+    if (nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0) return fail(RG_ERR_ARG, "bad size");
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    return rc ? rc : (int64_t)L.total;
+}
+
+extern "C" int rg_ctx_create(int device, rg_ctx **out)
+{
+    if (!out) return fail(RG_ERR_ARG, "out == NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(RG_ERR_CUDA, "no CUDA device (this library has no CPU path)", e);
+    if (device < 0 || device >= ndev) return fail(RG_ERR_ARG, "bad device index");
+    CK(cudaSetDevice(device));
+    rg_ctx *c = (rg_ctx *)calloc(1, sizeof(rg_ctx));
+    if (!c) return fail(RG_ERR_NOMEM, "calloc");
+    c->device = device;
+    e = cudaHostAlloc((void **)&c->h_status, CTR_WORDS * sizeof(uint32_t), cudaHostAllocDefault);
+    if (e != cudaSuccess) { free(c); return fail(RG_ERR_CUDA, "cudaHostAlloc", e); }
+    *out = c;
+    return RG_OK;
+}
+
+extern "C" void rg_ctx_destroy(rg_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->ws); cudaFree(c->d_image); cudaFree(c->d_mask); cudaFree(c->d_seeds);
+    cudaFreeHost(c->h_status);
+    free(c);
+}
+
+static int ensure_ws(rg_ctx *c, size_t bytes)
+{
+    if (bytes <= c->ws_bytes) return RG_OK;
+    CK(cudaSetDevice(c->device));
+    if (c->ws) { CK(cudaDeviceSynchronize()); cudaFree(c->ws); c->ws = nullptr; c->ws_bytes = 0; }
+    cudaError_t e = cudaMalloc(&c->ws, bytes);
+    if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(workspace)", e);
+    c->ws_bytes = bytes;
+    return RG_OK;
+}
+
+extern "C" int rg_ctx_reserve(rg_ctx *c, int64_t nx, int64_t ny, int64_t nz, int nseeds)
+{
+    if (!c || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0) return fail(RG_ERR_ARG, "bad argument");
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    if (rc) return rc;
+    return ensure_ws(c, L.total);
+}
+
+template <class C>
+static int set_attrs()
+{
+    CK(cudaFuncSetAttribute(k_pass_a<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
+    return RG_OK;
+}
+
+/* ------------------------------------------------------------------ the launch sequence */
+template <class C>
+static int launch_grow(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+                       int zlo_ext, int zhi_ext, const int32_t *d_seeds, int nseeds, int threshold,
+                       uint8_t *d_mask, cudaStream_t st)
+{
+    char *ws = (char *)c->ws;
+    Params P;
+    memset(&P, 0, sizeof P);
+    P.image = d_image; P.mask = d_mask; P.nx = nx; P.ny = ny; P.nz = nz;
+    P.ntx = L.ntx; P.nty = L.nty; P.ntz = L.ntz;
+    P.zlo_ext = zlo_ext; P.zhi_ext = zhi_ext;
+    P.tmode = threshold <= 0 ? 0 : threshold >= 256 ? 2 : 1;
+    P.t4 = (uint32_t)(threshold & 0xFF) * 0x01010101u;
+    P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
+    P.nseeds = nseeds;
+    P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
+    P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
+    P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
+    uint64_t *keys = (uint64_t *)(ws + L.off_keys), *keys2 = (uint64_t *)(ws + L.off_keys2);
+    P.seed_keys = keys;
+
+    int kb = nseeds > 0 ? (nseeds + 255) / 256 : 1; if (kb > 1024) kb = 1024;
+    k_seed_keys<C><<<kb, 256, 0, st>>>(P, d_seeds, keys);
+    if (nseeds > 2048) {
+        size_t tb = L.cub_bytes;
+        CK(cub::DeviceRadixSort::SortKeys(ws + L.off_cub, tb, keys, keys2, nseeds, 0, 64, st));
+        P.seed_keys = keys2;
+    } else if (nseeds > 1) {
+        k_sort_small<<<1, 1024, 0, st>>>(keys, nseeds);
+    }
+    k_pass_a<C><<<L.ntiles, RG_THREADS, sizeof(TileSmem<C>), st>>>(P);
+    int64_t items = (int64_t)L.ntiles * 3;
+    int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
+    k_merge<C><<<mb, 256, 0, st>>>(P);
+    k_pass_c<C><<<L.ntiles, RG_THREADS, sizeof(TileSmem<C>), st>>>(P);
+    CK(cudaGetLastError());
+    c->last_counters = P.counters; c->last_stream = st;
+    return RG_OK;
+}
+
+static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
+                            const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
+{
+    if (!c || !d_image || !d_mask || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !d_seeds))
+        return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    if (!c->attr_set) {
+        int rc = set_attrs<Cfg3D>(); if (rc) return rc;
+        rc = set_attrs<Cfg2D>(); if (rc) return rc;
+        c->attr_set = true;
+    }
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    if (rc) return rc;
+    rc = ensure_ws(c, L.total); if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    return nz == 1 ? launch_grow<Cfg2D>(c, L, d_image, nx, ny, nz, 0, 0, d_seeds, nseeds, threshold, d_mask, st)
+                   : launch_grow<Cfg3D>(c, L, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, st);
+}
+
+extern "C" int rg_grow_device(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+                              const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream)
+{
+    return grow_device_impl(c, d_image, nx, ny, nz, 0, 0, d_seeds_xyz, nseeds, threshold, d_mask, stream);
+}
+
+extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
+{
+    if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
+    CK(cudaSetDevice(c->device));
+    if (!c->last_counters) { if (stats) memset(stats, 0, 16); return RG_OK; }
+    CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
+    CK(cudaStreamSynchronize(c->last_stream));
+    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_FACE_MISMATCH]; stats[3] = 0; }
+    if (c->h_status[CTR_STATUS]) {
+        snprintf(g_err, sizeof g_err, "engine self-check failed: status=0x%x mismatching faces=%u", c->h_status[CTR_STATUS], c->h_status[CTR_FACE_MISMATCH]);
+        return RG_ERR_INTERNAL;
+    }
+    return RG_OK;
+}
+
+extern "C" int rg_apply_mask_device(rg_ctx *c, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream)
+{
+    if (!c || !d_image || !d_mask || n < 0) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    if (n == 0) return RG_OK;
+    int64_t b = (n + 255) / 256; if (b > 148 * 32) b = 148 * 32;
+    k_apply_mask<<<(int)b, 256, 0, (cudaStream_t)stream>>>(d_image, d_mask, n);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+/* ------------------------------------------------------------------ host-pointer entry points */
+static std::mutex g_mu;
+static rg_ctx *g_default[64];
+
+static int default_ctx(rg_ctx **out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(RG_ERR_CUDA, "no CUDA device (this library has no CPU path)", e);
+    if (dev < 0 || dev >= 64) return fail(RG_ERR_ARG, "device index");
+    if (!g_default[dev]) { int rc = rg_ctx_create(dev, &g_default[dev]); if (rc) return rc; }
+    *out = g_default[dev];
+    return RG_OK;
+}
+
+static int ensure_io(rg_ctx *c, size_t bytes, int nseeds)
+{
+    if (bytes > c->io_bytes) {
+        cudaFree(c->d_image); cudaFree(c->d_mask); c->d_image = c->d_mask = nullptr; c->io_bytes = 0;
+        cudaError_t e = cudaMalloc((void **)&c->d_image, bytes);
+        if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(image)", e);
+        e = cudaMalloc((void **)&c->d_mask, bytes);
+        if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(mask)", e);
+        c->io_bytes = bytes;
+    }
+    if ((size_t)nseeds > c->seeds_cap) {
+        cudaFree(c->d_seeds); c->d_seeds = nullptr; c->seeds_cap = 0;
+        size_t cap = (size_t)nseeds < 64 ? 64 : (size_t)nseeds;
+        cudaError_t e = cudaMalloc((void **)&c->d_seeds, cap * 12);
+        if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(seeds)", e);
+        c->seeds_cap = cap;
+    }
+    return RG_OK;
+}
+
+static int grow_host(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
+                     int threshold, uint8_t *mask_out, uint8_t *image_inout_apply)
+{
+    if (!image || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !seeds)) return fail(RG_ERR_ARG, "bad argument");
+    std::lock_guard<std::mutex> lk(g_mu);
+    rg_ctx *c; int rc = default_ctx(&c); if (rc) return rc;
+    size_t bytes = (size_t)nx * ny * nz;
+    rc = ensure_io(c, bytes, nseeds); if (rc) return rc;
+    cudaStream_t st = 0;
+    CK(cudaMemcpyAsync(c->d_image, image, bytes, cudaMemcpyHostToDevice, st));
+    if (nseeds) CK(cudaMemcpyAsync(c->d_seeds, seeds, (size_t)nseeds * 12, cudaMemcpyHostToDevice, st));
+    rc = grow_device_impl(c, c->d_image, nx, ny, nz, 0, 0, c->d_seeds, nseeds, threshold, c->d_mask, st);
+    if (rc) return rc;
+    if (mask_out) CK(cudaMemcpyAsync(mask_out, c->d_mask, bytes, cudaMemcpyDeviceToHost, st));
+    if (image_inout_apply) {
+        rc = rg_apply_mask_device(c, c->d_image, c->d_mask, (int64_t)bytes, st); if (rc) return rc;
+        CK(cudaMemcpyAsync(image_inout_apply, c->d_image, bytes, cudaMemcpyDeviceToHost, st));
+    }
+    return rg_ctx_status(c, nullptr);
+}
+
+extern "C" int rg_grow(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
+                       const int32_t *seeds_xyz, int nseeds, int threshold, uint8_t *mask_out)
+{
+    if (!mask_out) return fail(RG_ERR_ARG, "mask_out == NULL");
+    return grow_host(image, nx, ny, nz, seeds_xyz, nseeds, threshold, mask_out, nullptr);
+}
+
+static unsigned char *grow_512(unsigned char *data)
+{
+    /* raycast.cu:11 DATA_DIM 512; :286/:775 seed; :275 threshold */
+    const int64_t D = 512;
+    const int32_t seed[3] = {50, 300, 300};
+    if (!data) { fail(RG_ERR_ARG, "data == NULL"); return nullptr; }
+    unsigned char *region = (unsigned char *)calloc(sizeof(unsigned char), (size_t)(D * D * D));
+    if (!region) { fail(RG_ERR_NOMEM, "calloc"); return nullptr; }
+    if (grow_host(data, D, D, D, seed, 1, 1, region, nullptr) != RG_OK) { free(region); return nullptr; }
+    return region;
+}
+extern "C" unsigned char *grow_region_gpu(unsigned char *data) { return grow_512(data); }
+extern "C" unsigned char *grow_region_gpu_shared(unsigned char *data) { return grow_512(data); }
+extern "C" unsigned char *grow_region_serial(unsigned char *data) { return grow_512(data); }
+
+extern "C" int rg_grow_region_2d(unsigned char *image, int width, int height, unsigned char *mask_out, int apply)
+{
+    if (!image || width <= 0 || height <= 0) return fail(RG_ERR_ARG, "bad argument");
+    /* region.c:450-490 in global 0-based pixels */
+    const int32_t seeds[12] = { 4, 4, 0, width - 6, 4, 0, width - 6, height - 6, 0, 4, height - 6, 0 };
+    return grow_host(image, width, height, 1, seeds, 4, 2 /* region.c:81 */, mask_out, apply ? image : nullptr);
+}

@@ -1,0 +1,97 @@
+/*
+ * rg_port.h -- the few primitives the engine's kernel bodies are written against.
+ *
+ * The kernel bodies in rg_core.h are compiled twice:
+ *   - by nvcc for sm_100a (the product: RG_FN = __device__, CUDA intrinsics and atomics);
+ *   - by g++ for tests/emu (a sequential, one-thread-at-a-time walk of the SAME bodies
+ *     used only by the `not gpu` logic tests; plain loads/stores stand in for atomics).
+ * There is no CPU execution path in the product library.
+ */
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+
+#if defined(__CUDACC__)
+#define RG_FN __device__ __forceinline__
+#define RG_MFN __device__ __forceinline__
+#define RG_DEVICE_BUILD 1
+#else
+#define RG_FN static inline
+#define RG_MFN inline
+#define RG_DEVICE_BUILD 0
+#include <string.h>
+#endif
+
+namespace rg {
+
+struct u32x4 { uint32_t x, y, z, w; };
+
+#if RG_DEVICE_BUILD
+RG_FN int popc(uint32_t x) { return __popc(x); }
+RG_FN int clz(uint32_t x) { return __clz((int)x); }
+RG_FN int ffs1(uint32_t x) { return __ffs((int)x); }          /* 1-based, 0 if x == 0 */
+/* per-byte |a-b| < t  ->  4-bit nibble (bit j <-> byte j); t4 = t replicated into 4 bytes, 1 <= t <= 255 */
+RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
+{
+    uint32_t m = __vcmpltu4(__vabsdiffu4(a, b), t4);          /* 0xFF per similar byte */
+    return ((m & 0x01010101u) * 0x01020408u) >> 24;           /* gather the 4 flags into bits 0..3 */
+}
+RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { return atomicOr(p, v); }
+RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
+RG_FN uint32_t atomic_max(uint32_t *p, uint32_t v) { return atomicMax(p, v); }
+RG_FN uint32_t cas32(uint32_t *p, uint32_t cmp, uint32_t val) { return atomicCAS(p, cmp, val); }
+RG_FN uint16_t cas16(uint16_t *p, uint16_t cmp, uint16_t val)
+{
+    return atomicCAS((unsigned short *)p, (unsigned short)cmp, (unsigned short)val);
+}
+RG_FN uint16_t ldv16(const uint16_t *p) { return *(const volatile uint16_t *)p; }
+RG_FN uint32_t ldv32(const uint32_t *p) { return *(const volatile uint32_t *)p; }
+RG_FN void stv16(uint16_t *p, uint16_t v) { *(volatile uint16_t *)p = v; }
+RG_FN void stv32(uint32_t *p, uint32_t v) { *(volatile uint32_t *)p = v; }
+RG_FN u32x4 ld128(const void *p) { uint4 v = *(const uint4 *)p; return u32x4{v.x, v.y, v.z, v.w}; }
+RG_FN void st128(void *p, u32x4 v) { *(uint4 *)p = make_uint4(v.x, v.y, v.z, v.w); }
+/* streaming global accesses: the image is read once per pass and the mask written once */
+RG_FN u32x4 ld128_stream(const void *p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return u32x4{v.x, v.y, v.z, v.w};
+}
+RG_FN void st128_stream(void *p, u32x4 v)
+{
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+#else
+RG_FN int popc(uint32_t x) { return __builtin_popcount(x); }
+RG_FN int clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+RG_FN int ffs1(uint32_t x) { return __builtin_ffs((int)x); }
+RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
+{
+    uint32_t r = 0; int t = (int)(t4 & 0xFF);
+    for (int j = 0; j < 4; j++) {
+        int x = (a >> (8 * j)) & 0xFF, y = (b >> (8 * j)) & 0xFF, d = x > y ? x - y : y - x;
+        if (d < t) r |= 1u << j;
+    }
+    return r;
+}
+RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o | v; return o; }
+RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o + v; return o; }
+RG_FN uint32_t atomic_max(uint32_t *p, uint32_t v) { uint32_t o = *p; if (v > o) *p = v; return o; }
+RG_FN uint32_t cas32(uint32_t *p, uint32_t cmp, uint32_t val) { uint32_t o = *p; if (o == cmp) *p = val; return o; }
+RG_FN uint16_t cas16(uint16_t *p, uint16_t cmp, uint16_t val) { uint16_t o = *p; if (o == cmp) *p = val; return o; }
+RG_FN uint16_t ldv16(const uint16_t *p) { return *p; }
+RG_FN uint32_t ldv32(const uint32_t *p) { return *p; }
+RG_FN void stv16(uint16_t *p, uint16_t v) { *p = v; }
+RG_FN void stv32(uint32_t *p, uint32_t v) { *p = v; }
+RG_FN u32x4 ld128(const void *p) { u32x4 v; memcpy(&v, p, 16); return v; }
+RG_FN void st128(void *p, u32x4 v) { memcpy(p, &v, 16); }
+RG_FN u32x4 ld128_stream(const void *p) { return ld128(p); }
+RG_FN void st128_stream(void *p, u32x4 v) { st128(p, v); }
+#endif
+
+/* 4 mask bits -> 4 bytes of 0/1 */
+RG_FN uint32_t expand4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+} // namespace rg

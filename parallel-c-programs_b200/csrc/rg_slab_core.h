@@ -1,0 +1,91 @@
+/*
+ * rg_slab_core.h -- kernel bodies of the multi-GPU (z-slab) path.
+ *
+ * Replaces the distributed half of 2-mpi-region-growing/region.c: exchange() (:250-353),
+ * add_halo_to_stack() (:355-387) and finished() (:435-440).  The reference swaps mask borders
+ * and re-floods until an all-reduce reports no progress, so its round count grows with the
+ * number of times a region crosses a partition boundary.  Here every rank labels its slab once
+ * (pass A + B of rg_core.h, with the slab's outer z faces treated as tile faces), then
+ *   export_interface   lists, for each cross-slab edge of a boundary plane, the LOCAL ROOT of the
+ *                      component on this side (both sides enumerate the same edges in the same
+ *                      order, exactly like two tiles sharing a face);
+ *   [all-gather of the lists: torch.distributed / NCCL over NVLink, done by the host layer]
+ *   resolve_*          every rank solves the small union-find over (rank, root) vertices
+ *                      redundantly -- vertex 0 is the shared "holds a seed" vertex -- and hooks
+ *                      its own roots that reach vertex 0 to its local node 0;
+ * and pass C runs unchanged.  One exchange, whatever the number of crossings.
+ */
+#pragma once
+#include "rg_core.h"
+
+namespace rg {
+
+/* side 0: ZM faces of the bottom tile layer; side 1: ZP faces of the top tile layer.
+ * tile_off[0..ntx*nty] = exclusive prefix of the per-tile entry counts (scratch, written here). */
+template <class C, class Exec>
+RG_FN void export_offsets(Exec &ex, const Params &P, int side, uint32_t *tile_off, uint32_t *count_out, uint32_t *scratch)
+{
+    const int nt = P.ntx * P.nty;
+    const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
+    const int f = side ? F_ZP : F_ZM;
+    uint32_t total = ex.scan32(nt, [&](int i) { return (uint32_t)P.rec[layer + (uint32_t)i].cnt[f]; }, tile_off, scratch);
+    if (ex.tid() == 0) { tile_off[nt] = total; *count_out = total; }
+}
+
+template <class C, class Exec>
+RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *tile_off, uint32_t *out_roots)
+{
+    const int nt = P.ntx * P.nty;
+    const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
+    const int f = side ? F_ZP : F_ZM;
+    ex.gpfor((int64_t)nt, [&](int64_t i) {
+        uint32_t tile = layer + (uint32_t)i;
+        const TileRec &rc = P.rec[tile];
+        uint32_t cnt = rc.cnt[f], off = 0;
+        for (int k = 0; k < f; k++) off += rc.cnt[k];
+        const uint16_t *e = P.ent + (size_t)tile * C::ENT_MAX + off;
+        uint32_t *o = out_roots + tile_off[i];
+        for (uint32_t k = 0; k < cnt; k++) o[k] = find32(P.nparent, rc.node_base + e[k]);
+    });
+}
+
+#if !RG_DEVICE_BUILD
+/* sequential convenience used by the emulator */
+template <class C, class Exec>
+RG_FN void export_interface(Exec &ex, const Params &P, int side, uint32_t *out_roots, uint32_t *count_out)
+{
+    const int nt = P.ntx * P.nty;
+    uint32_t *tile_off = new uint32_t[(size_t)nt + 1];
+    uint32_t scratch[40];
+    export_offsets<C>(ex, P, side, tile_off, count_out, scratch);
+    export_entries<C>(ex, P, side, tile_off, out_roots);
+    delete[] tile_off;
+}
+#endif
+
+RG_FN uint32_t xvertex(uint32_t root, uint32_t off) { return root ? off + root : 0u; }
+
+/* lazily initialise only the vertices that appear on an interface */
+template <class Exec>
+RG_FN void resolve_init(Exec &ex, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
+{
+    ex.gpfor((int64_t)n, [&](int64_t i) { uint32_t v = xvertex(roots[i], off); xpar[v] = v; });
+}
+
+template <class Exec>
+RG_FN void resolve_union(Exec &ex, uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint32_t *b, uint32_t offb, uint32_t n)
+{
+    ex.gpfor((int64_t)n, [&](int64_t i) { unite32(xpar, xvertex(a[i], offa), xvertex(b[i], offb)); });
+}
+
+/* hook this rank's roots that reached the shared seeded vertex to the local node 0 */
+template <class Exec>
+RG_FN void resolve_apply(Exec &ex, const Params &P, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
+{
+    ex.gpfor((int64_t)n, [&](int64_t i) {
+        uint32_t r = roots[i];
+        if (r && find32(xpar, off + r) == 0u) unite32(P.nparent, r, 0u);
+    });
+}
+
+} // namespace rg

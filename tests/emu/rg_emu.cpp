@@ -1,0 +1,188 @@
+/*
+ * tests/emu/rg_emu.cpp -- sequential walk of the engine's kernel bodies.  TEST CODE ONLY.
+ *
+ * Compiles parallel-c-programs_b200/csrc/rg_core.h with g++ (RG_FN = inline, plain memory ops
+ * instead of atomics) and runs pass A / B / C one "thread" at a time, one tile after another.
+ * It lets the `not gpu` tests check the engine's LOGIC (edge planes, face-list alignment,
+ * node bookkeeping, slab interfaces) against the oracle without a GPU, including with tiny tile
+ * shapes that put many tile faces inside small random grids.  It is not part of libb200rg.so
+ * and nothing in the product can reach it.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+#include "../../parallel-c-programs_b200/csrc/rg_core.h"
+#include "../../parallel-c-programs_b200/csrc/rg_slab_core.h"
+
+using namespace rg;
+
+struct HostExec {
+    int tid() const { return 0; }
+    template <class F> void pfor(int n, F f) { for (int i = 0; i < n; i++) f(i); }
+    template <class F> void gpfor(int64_t n, F f) { for (int64_t i = 0; i < n; i++) f(i); }
+    void sync() {}
+    template <class F> uint32_t scan16(int n, F count, uint16_t *out, uint32_t *)
+    {
+        uint32_t run = 0;
+        for (int i = 0; i < n; i++) { out[i] = (uint16_t)run; run += count(i); }
+        return run;
+    }
+    template <class F> uint32_t scan32(int n, F count, uint32_t *out, uint32_t *)
+    {
+        uint32_t run = 0;
+        for (int i = 0; i < n; i++) { out[i] = run; run += count(i); }
+        return run;
+    }
+};
+
+struct EmuState {
+    std::vector<TileRec> rec; std::vector<uint16_t> ent; std::vector<uint32_t> npar; std::vector<uint16_t> nrep;
+    std::vector<uint64_t> keys; uint32_t counters[CTR_WORDS];
+    Params P;
+};
+
+template <class C>
+static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, int zlo, int zhi,
+                      const int32_t *seeds, int nseeds, int T, uint8_t *mask)
+{
+    Params &P = E.P; memset(&P, 0, sizeof P);
+    P.image = image; P.mask = mask; P.nx = nx; P.ny = ny; P.nz = nz;
+    P.ntx = (int)((nx + C::TX - 1) / C::TX); P.nty = (int)((ny + C::TY - 1) / C::TY); P.ntz = (int)((nz + C::TZ - 1) / C::TZ);
+    P.zlo_ext = zlo; P.zhi_ext = zhi;
+    P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u;
+    P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
+    size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
+    size_t cap = 1 + ntiles * C::ENT_MAX + (size_t)nseeds;
+    E.rec.assign(ntiles, TileRec()); E.ent.assign(ntiles * C::ENT_MAX, 0); E.npar.assign(cap, 0xDEADBEEF); E.nrep.assign(cap, 0);
+    E.keys.assign((size_t)std::max(nseeds, 1), ~0ull);
+    P.rec = E.rec.data(); P.ent = E.ent.data(); P.nparent = E.npar.data(); P.nrep = E.nrep.data();
+    P.counters = E.counters; P.node_cap = (uint32_t)cap; P.nseeds = nseeds; P.seed_keys = E.keys.data();
+    HostExec ex;
+    reset_counters(P);
+    make_seed_keys<C>(ex, P, seeds, E.keys.data());
+    std::sort(E.keys.begin(), E.keys.begin() + nseeds);
+}
+
+template <class C> static void emu_label(EmuState &E)
+{
+    HostExec ex; const Params &P = E.P;
+    uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
+    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(16, (sizeof(TileSmem<C>) + 15) / 16 * 16);
+    for (uint32_t t = 0; t < ntiles; t++) { memset(s, 0xA5, sizeof *s); tile_pass_a<C>(ex, P, t, *s); }
+    merge_faces<C>(ex, P);
+    free(s);
+}
+template <class C> static void emu_finish(EmuState &E)
+{
+    HostExec ex; const Params &P = E.P;
+    uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
+    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(16, (sizeof(TileSmem<C>) + 15) / 16 * 16);
+    for (uint32_t t = 0; t < ntiles; t++) { memset(s, 0x5A, sizeof *s); tile_pass_c<C>(ex, P, t, *s); }
+    free(s);
+}
+
+template <class C>
+static int emu_grow_t(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds, int T,
+                      uint8_t *mask, uint32_t *stats)
+{
+    EmuState E;
+    emu_setup<C>(E, image, nx, ny, nz, 0, 0, seeds, nseeds, T, mask);
+    emu_label<C>(E);
+    emu_finish<C>(E);
+    if (stats) { stats[0] = E.counters[CTR_NODES]; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_FACE_MISMATCH]; stats[3] = (uint32_t)E.rec.size(); }
+    return E.counters[CTR_STATUS] ? -4 : 0;
+}
+
+typedef TileCfg<32, 4, 4> CfgS3;      /* tiny tiles: many faces inside small grids */
+typedef TileCfg<64, 8, 2> CfgT3;
+typedef TileCfg<32, 8, 1> CfgS2;
+
+/* cfg: 0 = product shapes (Cfg3D / Cfg2D by nz), 1 = tiny shapes, 2 = another 3-D shape */
+extern "C" int emu_grow(int cfg, const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
+                        int T, uint8_t *mask, uint32_t *stats)
+{
+    if (nz == 1) return cfg == 0 ? emu_grow_t<Cfg2D>(image, nx, ny, nz, seeds, nseeds, T, mask, stats)
+                                 : emu_grow_t<CfgS2>(image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+    if (cfg == 0) return emu_grow_t<Cfg3D>(image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+    if (cfg == 1) return emu_grow_t<CfgS3>(image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+    return emu_grow_t<CfgT3>(image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+}
+
+/* ---- multi-slab emulation: G logical ranks on one host, the same protocol as rgb200.SlabGrower ---- */
+template <class C>
+static int emu_grow_slabs_t(int G, const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
+                            int T, uint8_t *mask, uint32_t *stats)
+{
+    std::vector<EmuState> E((size_t)G);
+    std::vector<int64_t> zb((size_t)G + 1);
+    for (int g = 0; g <= G; g++) zb[(size_t)g] = nz * g / G;
+    std::vector<std::vector<int32_t>> sl((size_t)G);
+    HostExec ex;
+    /* each rank: local seeds (shifted to slab coordinates), pass A + B on its slab */
+    for (int g = 0; g < G; g++) {
+        int64_t z0 = zb[(size_t)g], z1 = zb[(size_t)g + 1];
+        if (z1 <= z0) continue;
+        for (int i = 0; i < nseeds; i++) {
+            int32_t z = seeds[3 * i + 2];
+            if (z >= z0 && z < z1) { sl[(size_t)g].push_back(seeds[3 * i]); sl[(size_t)g].push_back(seeds[3 * i + 1]); sl[(size_t)g].push_back((int32_t)(z - z0)); }
+        }
+        int zlo = 0, zhi = 0;
+        for (int h = 0; h < g; h++) if (zb[(size_t)h + 1] > zb[(size_t)h]) zlo = 1;
+        for (int h = g + 1; h < G; h++) if (zb[(size_t)h + 1] > zb[(size_t)h]) zhi = 1;
+        emu_setup<C>(E[(size_t)g], image + z0 * nx * ny, nx, ny, z1 - z0, zlo, zhi, sl[(size_t)g].data(), (int)sl[(size_t)g].size() / 3, T,
+                     mask + z0 * nx * ny);
+        emu_label<C>(E[(size_t)g]);
+    }
+    /* export interface lists (roots), "all-gather", resolve redundantly, then pass C */
+    std::vector<std::vector<uint32_t>> lo((size_t)G), hi((size_t)G);
+    std::vector<int> live;
+    for (int g = 0; g < G; g++) if (zb[(size_t)g + 1] > zb[(size_t)g]) live.push_back(g);
+    for (int g : live) {
+        const Params &P = E[(size_t)g].P;
+        size_t cap = (size_t)P.ntx * P.nty * C::FZN + 1;
+        lo[(size_t)g].assign(cap, 0); hi[(size_t)g].assign(cap, 0);
+        uint32_t nlo = 0, nhi = 0;
+        if (P.zlo_ext) export_interface<C>(ex, P, 0, lo[(size_t)g].data(), &nlo);
+        if (P.zhi_ext) export_interface<C>(ex, P, 1, hi[(size_t)g].data(), &nhi);
+        lo[(size_t)g].resize(nlo); hi[(size_t)g].resize(nhi);
+    }
+    int rc = 0;
+    for (size_t li = 0; li + 1 < live.size(); li++)
+        if (hi[(size_t)live[li]].size() != lo[(size_t)live[li + 1]].size()) rc = -4;
+    if (!rc) {
+        /* global vertex ids: offset[g] + local root; vertex 0 of every rank is the shared "seeded" vertex */
+        std::vector<uint32_t> off(live.size() + 1, 1);
+        for (size_t li = 0; li < live.size(); li++) off[li + 1] = off[li] + E[(size_t)live[li]].counters[CTR_NODES];
+        std::vector<uint32_t> xpar(off.back(), 0);
+        for (size_t li = 0; li + 1 < live.size(); li++) {
+            const std::vector<uint32_t> &a = hi[(size_t)live[li]], &b = lo[(size_t)live[li + 1]];
+            xpar[0] = 0;
+            resolve_init(ex, xpar.data(), a.data(), (uint32_t)a.size(), off[li]);
+            resolve_init(ex, xpar.data(), b.data(), (uint32_t)b.size(), off[li + 1]);
+        }
+        for (size_t li = 0; li + 1 < live.size(); li++) {
+            const std::vector<uint32_t> &a = hi[(size_t)live[li]], &b = lo[(size_t)live[li + 1]];
+            resolve_union(ex, xpar.data(), a.data(), off[li], b.data(), off[li + 1], (uint32_t)a.size());
+        }
+        for (size_t li = 0; li < live.size(); li++) {
+            int g = live[li];
+            resolve_apply(ex, E[(size_t)g].P, xpar.data(), lo[(size_t)g].data(), (uint32_t)lo[(size_t)g].size(), off[li]);
+            resolve_apply(ex, E[(size_t)g].P, xpar.data(), hi[(size_t)g].data(), (uint32_t)hi[(size_t)g].size(), off[li]);
+        }
+    }
+    uint32_t st = 0, nodes = 0;
+    for (int g : live) { emu_finish<C>(E[(size_t)g]); st |= E[(size_t)g].counters[CTR_STATUS]; nodes += E[(size_t)g].counters[CTR_NODES]; }
+    if (stats) { stats[0] = nodes; stats[1] = st; stats[2] = 0; stats[3] = (uint32_t)live.size(); }
+    return (rc || st) ? -4 : 0;
+}
+
+extern "C" int emu_grow_slabs(int cfg, int G, const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
+                              int T, uint8_t *mask, uint32_t *stats)
+{
+    if (nz == 1 || G < 1) return -1;
+    if (cfg == 0) return emu_grow_slabs_t<Cfg3D>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+    if (cfg == 1) return emu_grow_slabs_t<CfgS3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+    return emu_grow_slabs_t<CfgT3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
+}

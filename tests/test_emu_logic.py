@@ -1,0 +1,122 @@
+"""Engine LOGIC on the CPU: the kernel bodies of rg_core.h / rg_slab_core.h, walked sequentially by
+tests/emu (test code, not part of the product), against the oracle.  Tiny tile shapes put many tile
+faces, partial tiles and slab interfaces inside small random grids."""
+import ctypes, os, subprocess
+import numpy as np
+import pytest
+from conftest import ROOT
+
+u8p = ctypes.c_void_p
+
+
+@pytest.fixture(scope="module")
+def emu():
+    d = os.path.join(ROOT, "tests", "emu")
+    subprocess.check_call(["make", "-s", "-C", d])
+    L = ctypes.CDLL(os.path.join(d, "librg_emu.so"))
+    L.emu_grow.argtypes = [ctypes.c_int, u8p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                           ctypes.c_int, u8p, ctypes.c_void_p]
+    L.emu_grow_slabs.argtypes = [ctypes.c_int, ctypes.c_int, u8p, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p,
+                                 ctypes.c_int, ctypes.c_int, u8p, ctypes.c_void_p]
+    return L
+
+
+def run_emu(L, cfg, img, seeds, T, slabs=0):
+    img = np.ascontiguousarray(img, np.uint8)
+    nz, ny, nx = (1,) + img.shape if img.ndim == 2 else img.shape
+    seeds = np.ascontiguousarray(np.asarray(seeds, np.int32).reshape(-1, 3))
+    mask = np.full(img.shape, 7, np.uint8)
+    stats = np.zeros(4, np.uint32)
+    if slabs:
+        rc = L.emu_grow_slabs(cfg, slabs, img.ctypes.data, nx, ny, nz, seeds.ctypes.data, len(seeds), T, mask.ctypes.data, stats.ctypes.data)
+    else:
+        rc = L.emu_grow(cfg, img.ctypes.data, nx, ny, nz, seeds.ctypes.data, len(seeds), T, mask.ctypes.data, stats.ctypes.data)
+    assert rc == 0, (rc, stats)
+    return mask, stats
+
+
+def rand_case(rng, shape, levels, nseeds):
+    img = rng.integers(0, levels, size=shape, dtype=np.uint8)
+    dims = shape[::-1] if len(shape) == 3 else (shape[1], shape[0], 1)
+    seeds = np.stack([rng.integers(-1, d + 1, size=nseeds) for d in dims], 1).astype(np.int32)
+    if len(shape) == 2:
+        seeds[:, 2] = 0
+    return img, seeds
+
+
+@pytest.mark.parametrize("cfg", [1, 2])
+@pytest.mark.parametrize("shape", [(9, 10, 70), (8, 8, 64), (5, 13, 33), (16, 4, 32), (1, 1, 1), (2, 9, 100), (12, 12, 12)])
+@pytest.mark.parametrize("levels,T", [(3, 1), (6, 2), (2, 1), (40, 3)])
+def test_emu_3d_tiny_tiles(emu, oracle, cfg, shape, levels, T):
+    rng = np.random.default_rng(abs(hash((cfg, shape, levels, T))) % 2**32)
+    img, seeds = rand_case(rng, shape, levels, 6)
+    got, _ = run_emu(emu, cfg, img, seeds, T)
+    assert (got == oracle.grow(img, seeds, T)).all()
+
+
+@pytest.mark.parametrize("shape", [(20, 70), (8, 32), (33, 33), (1, 5), (17, 128), (64, 31)])
+@pytest.mark.parametrize("levels,T", [(3, 1), (6, 2), (2, 1)])
+def test_emu_2d_tiny_tiles(emu, oracle, shape, levels, T):
+    rng = np.random.default_rng(abs(hash((shape, levels, T))) % 2**32)
+    img, seeds = rand_case(rng, shape, levels, 5)
+    got, _ = run_emu(emu, 1, img, seeds, T)
+    assert (got == oracle.grow(img, seeds, T)).all()
+
+
+@pytest.mark.parametrize("T", [0, 1, 255, 256, 300, -3])
+def test_emu_threshold_extremes(emu, oracle, T):
+    rng = np.random.default_rng(5 + abs(T))
+    img = rng.integers(0, 256, size=(6, 9, 40), dtype=np.uint8)
+    seeds = [[0, 0, 0], [39, 8, 5]]
+    got, _ = run_emu(emu, 1, img, seeds, T)
+    assert (got == oracle.grow(img, seeds, T)).all()
+
+
+def test_emu_product_tile_shapes(emu, oracle):
+    """the real 64x32x16 and 128x256 tiles, on grids a little larger than one tile"""
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 3, size=(20, 40, 100), dtype=np.uint8)
+    seeds = [[1, 1, 1], [99, 39, 19], [64, 32, 16], [63, 31, 15]]
+    got, st = run_emu(emu, 0, img, seeds, 1)
+    assert (got == oracle.grow(img, seeds, 1)).all()
+    img2 = rng.integers(0, 4, size=(300, 200), dtype=np.uint8)
+    seeds2 = [[4, 4, 0], [194, 4, 0], [194, 294, 0], [4, 294, 0]]
+    got2, _ = run_emu(emu, 0, img2, seeds2, 2)
+    assert (got2 == oracle.grow(img2, seeds2, 2)).all()
+
+
+def test_emu_no_seeds_and_all_dropped(emu, oracle):
+    img = np.zeros((4, 4, 32), np.uint8)
+    got, _ = run_emu(emu, 1, img, np.zeros((0, 3), np.int32), 1)
+    assert not got.any()
+    got, _ = run_emu(emu, 1, img, [[-1, 0, 0], [32, 0, 0], [0, 4, 0], [0, 0, 4]], 1)
+    assert not got.any()
+    got, _ = run_emu(emu, 1, img, [[31, 3, 3]], 1)
+    assert got.all()
+
+
+@pytest.mark.parametrize("kind,n", [("c3", 24), ("c3", 33), ("c1h", 64), ("c4", 64), ("c2", 128)])
+def test_emu_synthetic_shapes(emu, oracle, kind, n):
+    img, seeds, T = oracle.synth(kind, n, 0x5EED0000)
+    got, _ = run_emu(emu, 1, img, seeds, T)
+    assert (got == oracle.grow(img, seeds, T)).all()
+
+
+@pytest.mark.parametrize("G", [2, 3, 4, 8])
+@pytest.mark.parametrize("cfg", [1, 2])
+def test_emu_slabs_random(emu, oracle, G, cfg):
+    rng = np.random.default_rng(100 * G + cfg)
+    img, seeds = rand_case(rng, (19, 10, 70), 3, 6)
+    got, st = run_emu(emu, cfg, img, seeds, 1, slabs=G)
+    assert (got == oracle.grow(img, seeds, 1)).all()
+
+
+@pytest.mark.parametrize("G", [2, 4, 8, 11])
+def test_emu_slabs_serpentine(emu, oracle, G):
+    """C4's z-serpentine crosses every slab interface many times: one exchange must be enough"""
+    img, seeds, T = oracle.synth("c4", 64, 0x5EED0004)
+    got, _ = run_emu(emu, 1, img, seeds, T, slabs=G)
+    assert (got == oracle.grow(img, seeds, T)).all()
+    img, seeds, T = oracle.synth("c3", 20)
+    got, _ = run_emu(emu, 2, img, seeds, T, slabs=G)
+    assert (got == oracle.grow(img, seeds, T)).all()
