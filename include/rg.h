@@ -81,10 +81,49 @@ int rg_grow_device(rg_ctx *ctx, const uint8_t *d_image, int64_t nx, int64_t ny, 
  * stats (may be NULL) receives {nodes, status bits, mismatching faces, 0}. */
 int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);
 
+/* Optional per-kernel timing with CUDA events on the launching stream (used by bench.py for the
+ * roofline of the dominant kernel).  ms = {seed sort, pass A, pass B, pass C} of the last grow.
+ * Stands in for the gettimeofday()/print_time() pair around the grow call, raycast.cu:23-27,832-836. */
+int rg_ctx_profile(rg_ctx *ctx, int enable);
+int rg_ctx_profile_read(rg_ctx *ctx, float ms[4]);
+
 /* replaces write_image()'s loop, region.c:575-577, on the device: image[i] *= (mask[i] == 0). */
 int rg_apply_mask_device(rg_ctx *ctx, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream);
 
 const char *rg_last_error(void);
+
+/* ---- z-slab (multi-GPU) phases ------------------------------------------------------------- */
+/* Together these replace the distributed half of 2-mpi-region-growing/region.c -- exchange()
+ * (:250-353), add_halo_to_stack() (:355-387), finished() (:435-440) and the static image-halo
+ * scatter distribute_image_halo() (:145-246) -- for one rank that owns planes [z0, z0+nz_local)
+ * of the volume.  One process per GPU; the host layer (rgb200.SlabGrower, torch.distributed over
+ * NCCL) moves the interface lists between ranks.  Sequence per rank:
+ *   rg_slab_label -> rg_slab_export(side 0/1) -> [all-gather counts, lists] ->
+ *   rg_slab_resolve_init (every list) -> rg_slab_resolve_union (every interface) ->
+ *   rg_slab_resolve_apply (own two lists) -> rg_slab_finish.
+ * One exchange, independent of how often a region crosses slab boundaries (the reference needs a
+ * round per crossing). */
+
+/* d_slab points at the slab's first own plane; if has_lower / has_upper the image planes just
+ * below / above it (the neighbour's boundary planes, cf. distribute_image_halo) must be readable
+ * at d_slab - nx*ny and d_slab + nz_local*nx*ny.  Seeds are slab-local (z - z0) and only those
+ * inside the slab.  Enqueues seed sort + pass A + pass B. */
+int rg_slab_label(rg_ctx *ctx, const uint8_t *d_slab, int64_t nx, int64_t ny, int64_t nz_local,
+                  int has_lower, int has_upper, const int32_t *d_seeds_xyz, int nseeds, int threshold,
+                  uint8_t *d_mask_slab, void *stream);
+/* worst-case number of entries of one interface list (size the export buffers with it) */
+int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny);
+/* side 0 = interface with the lower rank, 1 = with the upper rank.  d_roots_out receives, for every
+ * cross-slab edge in canonical order, the local root node on this side; d_counts3[side] the
+ * number of entries and d_counts3[2] the rank's node count. */
+int rg_slab_export(rg_ctx *ctx, int side, uint32_t *d_roots_out, uint32_t *d_counts3, void *stream);
+/* union-find over (rank, root) vertices: vertex = root ? vertex_offset(rank) + root : 0 */
+int rg_slab_resolve_init(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_roots, uint32_t n, uint32_t vertex_offset, void *stream);
+int rg_slab_resolve_union(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_upper_of_lower_rank, uint32_t off_lower_rank,
+                          const uint32_t *d_lower_of_upper_rank, uint32_t off_upper_rank, uint32_t n, void *stream);
+int rg_slab_resolve_apply(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_own_roots, uint32_t n, uint32_t own_vertex_offset, void *stream);
+/* pass C on the slab labelled last */
+int rg_slab_finish(rg_ctx *ctx, void *stream);
 
 /* ---- synthetic inputs on the device (replaces func()/create_data(), raycast.cu:114-158) ---- */
 /* kind: 1 = exercise geometry with hash noise (C1h), 2 = C2 image (n x n), 3 = C3 serpentine,

@@ -13,6 +13,7 @@
 #include <mutex>
 
 #include "rg_core.h"
+#include "rg_slab_core.h"
 #include "../../include/rg.h"
 
 using namespace rg;
@@ -30,7 +31,7 @@ struct DevExec {
     }
     __device__ __forceinline__ void sync() { __syncthreads(); }
     /* block-wide exclusive scan of count(i), i < n, into out[i]; returns the total to every thread */
-    template <class F> __device__ __forceinline__ uint32_t scan16(int n, F count, uint16_t *out, uint32_t *scratch)
+    template <class T, class F> __device__ __forceinline__ uint32_t scan(int n, F count, T *out, uint32_t *scratch)
     {
         const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
         uint32_t base = 0;
@@ -49,12 +50,14 @@ struct DevExec {
                 if (lane == 31) scratch[32] = inc2;
             }
             __syncthreads();
-            if (i < n) out[i] = (uint16_t)(base + scratch[wid] + incl - c);
+            if (i < n) out[i] = (T)(base + scratch[wid] + incl - c);
             base += scratch[32];
             __syncthreads();
         }
         return base;
     }
+    template <class F> __device__ __forceinline__ uint32_t scan16(int n, F count, uint16_t *out, uint32_t *scratch) { return scan<uint16_t>(n, count, out, scratch); }
+    template <class F> __device__ __forceinline__ uint32_t scan32(int n, F count, uint32_t *out, uint32_t *scratch) { return scan<uint32_t>(n, count, out, scratch); }
 };
 
 /* ------------------------------------------------------------------ kernels */
@@ -119,6 +122,38 @@ __global__ void __launch_bounds__(256) k_apply_mask(uint8_t *image, const uint8_
     for (; i < n; i += stride) if (mask[i]) image[i] = 0;
 }
 
+/* multi-GPU (z-slab) path, bodies in rg_slab_core.h */
+template <class C>
+__global__ void __launch_bounds__(1024) k_export_offsets(const Params P, int side, uint32_t *tile_off, uint32_t *count_out)
+{
+    __shared__ uint32_t scratch[40];
+    DevExec ex;
+    export_offsets<C>(ex, P, side, tile_off, count_out, scratch);
+}
+template <class C>
+__global__ void __launch_bounds__(128) k_export_entries(const Params P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t *counts3)
+{
+    DevExec ex;
+    if (blockIdx.x == 0 && threadIdx.x == 0) counts3[2] = P.counters[CTR_NODES];
+    export_entries<C>(ex, P, side, tile_off, out_roots);
+}
+__global__ void __launch_bounds__(256) k_resolve_init(uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
+{
+    DevExec ex;
+    if (blockIdx.x == 0 && threadIdx.x == 0) xpar[0] = 0;
+    resolve_init(ex, xpar, roots, n, off);
+}
+__global__ void __launch_bounds__(256) k_resolve_union(uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint32_t *b, uint32_t offb, uint32_t n)
+{
+    DevExec ex;
+    resolve_union(ex, xpar, a, offa, b, offb, n);
+}
+__global__ void __launch_bounds__(256) k_resolve_apply(const Params P, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
+{
+    DevExec ex;
+    resolve_apply(ex, P, xpar, roots, n, off);
+}
+
 /* ------------------------------------------------------------------ errors */
 static thread_local char g_err[512] = "";
 static int fail(int code, const char *what, cudaError_t e = cudaSuccess)
@@ -141,10 +176,13 @@ struct rg_ctx {
     uint32_t *last_counters;                   /* device counters of the last call */
     cudaStream_t last_stream;
     bool attr_set;
+    Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
+    uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
+    bool profile; cudaEvent_t ev[5]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
 };
 
 struct Layout {
-    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, total;
+    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, total;
     uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
 };
 
@@ -174,6 +212,8 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
         L.cub_bytes = tb;
     }
     L.off_cub = o; o = align_up(o + L.cub_bytes, 256);
+    L.off_if0 = o; o = align_up(o + ((size_t)ntx * nty + 1) * 4, 256);
+    L.off_if1 = o; o = align_up(o + ((size_t)ntx * nty + 1) * 4, 256);
     L.total = o;
     return RG_OK;
 }
@@ -213,6 +253,7 @@ extern "C" void rg_ctx_destroy(rg_ctx *c)
     cudaSetDevice(c->device);
     cudaFree(c->ws); cudaFree(c->d_image); cudaFree(c->d_mask); cudaFree(c->d_seeds);
     cudaFreeHost(c->h_status);
+    if (c->ev_made) for (int i = 0; i < 5; i++) cudaEventDestroy(c->ev[i]);
     free(c);
 }
 
@@ -245,7 +286,7 @@ static int set_attrs()
 
 /* ------------------------------------------------------------------ the launch sequence */
 template <class C>
-static int launch_grow(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
                        int zlo_ext, int zhi_ext, const int32_t *d_seeds, int nseeds, int threshold,
                        uint8_t *d_mask, cudaStream_t st)
 {
@@ -266,6 +307,7 @@ static int launch_grow(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64
     P.seed_keys = keys;
 
     int kb = nseeds > 0 ? (nseeds + 255) / 256 : 1; if (kb > 1024) kb = 1024;
+    if (c->profile) cudaEventRecord(c->ev[0], st);
     k_seed_keys<C><<<kb, 256, 0, st>>>(P, d_seeds, keys);
     if (nseeds > 2048) {
         size_t tb = L.cub_bytes;
@@ -274,17 +316,32 @@ static int launch_grow(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64
     } else if (nseeds > 1) {
         k_sort_small<<<1, 1024, 0, st>>>(keys, nseeds);
     }
+    if (c->profile) cudaEventRecord(c->ev[1], st);
     k_pass_a<C><<<L.ntiles, RG_THREADS, sizeof(TileSmem<C>), st>>>(P);
+    if (c->profile) cudaEventRecord(c->ev[2], st);
     int64_t items = (int64_t)L.ntiles * 3;
     int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
     k_merge<C><<<mb, 256, 0, st>>>(P);
-    k_pass_c<C><<<L.ntiles, RG_THREADS, sizeof(TileSmem<C>), st>>>(P);
+    if (c->profile) cudaEventRecord(c->ev[3], st);
     CK(cudaGetLastError());
     c->last_counters = P.counters; c->last_stream = st;
+    c->last_P = P; c->last_is2d = (C::TZ == 1); c->last_ntiles = L.ntiles; c->have_last = true;
+    c->if_off[0] = (uint32_t *)(ws + L.off_if0); c->if_off[1] = (uint32_t *)(ws + L.off_if1);
     return RG_OK;
 }
 
-static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
+static int launch_finish(rg_ctx *c, cudaStream_t st)
+{
+    if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
+    if (c->last_is2d) k_pass_c<Cfg2D><<<c->last_ntiles, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P);
+    else k_pass_c<Cfg3D><<<c->last_ntiles, RG_THREADS, sizeof(TileSmem<Cfg3D>), st>>>(c->last_P);
+    if (c->profile) cudaEventRecord(c->ev[4], st);
+    CK(cudaGetLastError());
+    c->last_stream = st;
+    return RG_OK;
+}
+
+static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
                             const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
 {
     if (!c || !d_image || !d_mask || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !d_seeds))
@@ -299,8 +356,84 @@ static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64
     if (rc) return rc;
     rc = ensure_ws(c, L.total); if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    return nz == 1 ? launch_grow<Cfg2D>(c, L, d_image, nx, ny, nz, 0, 0, d_seeds, nseeds, threshold, d_mask, st)
-                   : launch_grow<Cfg3D>(c, L, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, st);
+    return nz == 1 ? launch_label<Cfg2D>(c, L, d_image, nx, ny, nz, 0, 0, d_seeds, nseeds, threshold, d_mask, st)
+                   : launch_label<Cfg3D>(c, L, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, st);
+}
+
+static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
+                            const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
+{
+    int rc = label_device_impl(c, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, stream);
+    if (rc) return rc;
+    return launch_finish(c, (cudaStream_t)stream);
+}
+
+/* ------------------------------------------------------------------ z-slab (multi-GPU) phases */
+extern "C" int rg_slab_label(rg_ctx *c, const uint8_t *d_slab, int64_t nx, int64_t ny, int64_t nz_local, int has_lower, int has_upper,
+                             const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask_slab, void *stream)
+{
+    if (nz_local < 1) return fail(RG_ERR_ARG, "empty slab");
+    if (nz_local == 1 && (has_lower || has_upper)) return fail(RG_ERR_ARG, "one-plane slabs cannot have neighbours (use >= 2 planes per rank)");
+    return label_device_impl(c, d_slab, nx, ny, nz_local, has_lower ? 1 : 0, has_upper ? 1 : 0, d_seeds_xyz, nseeds, threshold, d_mask_slab, stream);
+}
+
+extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny)
+{
+    int64_t ntx = (nx + Cfg3D::TX - 1) / Cfg3D::TX, nty = (ny + Cfg3D::TY - 1) / Cfg3D::TY;
+    return ntx * nty * (int64_t)Cfg3D::FZN;
+}
+
+extern "C" int rg_slab_export(rg_ctx *c, int side, uint32_t *d_roots_out, uint32_t *d_counts3, void *stream)
+{
+    if (!c || !c->have_last || c->last_is2d || !d_roots_out || !d_counts3 || side < 0 || side > 1) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const Params &P = c->last_P;
+    int nt = P.ntx * P.nty;
+    k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_counts3 + side);
+    int b = (nt + 127) / 128;
+    k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots_out, d_counts3);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+static int blocks_for(uint32_t n) { int b = (int)((n + 255u) / 256u); return b < 1 ? 1 : b > 148 * 16 ? 148 * 16 : b; }
+
+extern "C" int rg_slab_resolve_init(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_roots, uint32_t n, uint32_t vertex_offset, void *stream)
+{
+    if (!c || !d_xpar || (n && !d_roots)) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    k_resolve_init<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(d_xpar, d_roots, n, vertex_offset);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_resolve_union(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_upper_of_lower_rank, uint32_t off_lower_rank,
+                                     const uint32_t *d_lower_of_upper_rank, uint32_t off_upper_rank, uint32_t n, void *stream)
+{
+    if (!c || !d_xpar || (n && (!d_upper_of_lower_rank || !d_lower_of_upper_rank))) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    if (!n) return RG_OK;
+    k_resolve_union<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(d_xpar, d_upper_of_lower_rank, off_lower_rank, d_lower_of_upper_rank, off_upper_rank, n);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_resolve_apply(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_own_roots, uint32_t n, uint32_t own_vertex_offset, void *stream)
+{
+    if (!c || !c->have_last || !d_xpar || (n && !d_own_roots)) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    if (!n) return RG_OK;
+    k_resolve_apply<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(c->last_P, d_xpar, d_own_roots, n, own_vertex_offset);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_finish(rg_ctx *c, void *stream)
+{
+    if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
+    CK(cudaSetDevice(c->device));
+    return launch_finish(c, (cudaStream_t)stream);
 }
 
 extern "C" int rg_grow_device(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
@@ -321,6 +454,24 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
         snprintf(g_err, sizeof g_err, "engine self-check failed: status=0x%x mismatching faces=%u", c->h_status[CTR_STATUS], c->h_status[CTR_FACE_MISMATCH]);
         return RG_ERR_INTERNAL;
     }
+    return RG_OK;
+}
+
+extern "C" int rg_ctx_profile(rg_ctx *c, int enable)
+{
+    if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
+    CK(cudaSetDevice(c->device));
+    if (enable && !c->ev_made) { for (int i = 0; i < 5; i++) CK(cudaEventCreate(&c->ev[i])); c->ev_made = true; }
+    c->profile = enable != 0;
+    return RG_OK;
+}
+
+extern "C" int rg_ctx_profile_read(rg_ctx *c, float ms[4])
+{
+    if (!c || !ms || !c->ev_made) return fail(RG_ERR_ARG, "profiling was not enabled");
+    CK(cudaSetDevice(c->device));
+    CK(cudaEventSynchronize(c->ev[4]));
+    for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms[i], c->ev[i], c->ev[i + 1]));
     return RG_OK;
 }
 

@@ -1,0 +1,145 @@
+"""Multi-rank z-slab driver: one process per GPU, torch.distributed for the plumbing.
+
+Mirrors the distributed half of the reference's 2-D MPI program (2-mpi-region-growing/region.c):
+  distribute_image_halo (:145-246)  -> exchange_image_halos(): one static boundary-plane swap
+  exchange + add_halo_to_stack + finished (:250-387, :435-440), repeated until no rank progresses
+                                    -> ONE all-gather of interface root lists + a redundant
+                                       union-find on every rank (rg_slab_* in include/rg.h)
+The per-rank compute is the same CUDA engine as the single-GPU path.  `lib` is libb200rg.so; the
+CPU logic tests pass the sequential emulator (tests/emu) with CPU tensors and the gloo backend --
+this module never picks a CPU implementation on its own.
+"""
+import ctypes
+
+import numpy as np
+
+
+def slab_bounds(nz, rank, world):
+    """slab k = z in [floor(k*nz/G), floor((k+1)*nz/G))  """
+    return nz * rank // world, nz * (rank + 1) // world
+
+
+class SlabGrower:
+    def __init__(self, lib, ctx_handle, nx, ny, nz, rank, world, device, group=None, use_cuda_stream=True):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.lib, self.ctx = lib, ctx_handle
+        self.nx, self.ny, self.nz = int(nx), int(ny), int(nz)
+        self.rank, self.world, self.group = int(rank), int(world), group
+        self.device = device
+        self.use_cuda_stream = use_cuda_stream
+        self.z0, self.z1 = slab_bounds(self.nz, self.rank, self.world)
+        self.nzl = self.z1 - self.z0
+        if self.world > 1 and self.nzl < 2:
+            raise ValueError("each rank needs at least 2 planes")
+        self.has_lower = self.rank > 0
+        self.has_upper = self.rank < self.world - 1
+        plane = self.nx * self.ny
+        # slab with one halo plane on each side (present even when unused: keeps offsets simple)
+        self.buf = torch.zeros((self.nzl + 2) * plane, dtype=torch.uint8, device=device)
+        self.image = self.buf[plane:(self.nzl + 1) * plane].view(self.nzl, self.ny, self.nx)
+        self.mask = torch.empty((self.nzl, self.ny, self.nx), dtype=torch.uint8, device=device)
+        if self.world > 1:
+            cap = int(lib.rg_slab_interface_capacity(self.nx, self.ny))
+            self.cap = cap
+            self.lists = torch.zeros((2, cap), dtype=torch.int32, device=device)
+            self.counts = torch.zeros(4, dtype=torch.int32, device=device)
+            self.all_counts = torch.zeros(self.world * 4, dtype=torch.int32, device=device)   # flat: gloo wants 1-D
+        self.seeds_dev, self.nseeds = None, 0
+        self.rounds = 0
+
+    # ---- helpers
+    def _stream(self):
+        if self.use_cuda_stream:
+            return ctypes.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+        return None
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            msg = self.lib.rg_last_error()
+            raise RuntimeError(f"{what} failed with {rc}: {msg.decode() if msg else ''}")
+
+    def set_seeds(self, seeds_global):
+        """keep the seeds that fall into this slab, in slab-local z (add_seeds, region.c:450-490:
+        only the owning rank takes a seed)"""
+        s = np.asarray(seeds_global, np.int64).reshape(-1, 3)
+        keep = (s[:, 2] >= self.z0) & (s[:, 2] < self.z1)
+        loc = s[keep].copy()
+        loc[:, 2] -= self.z0
+        self.nseeds = int(len(loc))
+        self.seeds_dev = self.torch.tensor(loc.astype(np.int32).reshape(-1, 3), dtype=self.torch.int32,
+                                           device=self.device).contiguous() if self.nseeds else None
+
+    def exchange_image_halos(self):
+        """static, once per image: my top plane -> upper rank's lower halo, my bottom plane -> lower
+        rank's upper halo (distribute_image_halo, region.c:145-246)"""
+        if self.world == 1:
+            return
+        dist, plane = self.dist, self.nx * self.ny
+        ops = []
+        lo_halo = self.buf[:plane]
+        hi_halo = self.buf[(self.nzl + 1) * plane:]
+        first = self.buf[plane:2 * plane]
+        last = self.buf[self.nzl * plane:(self.nzl + 1) * plane]
+        if self.has_upper:
+            ops.append(dist.P2POp(dist.isend, last, self.rank + 1, self.group))
+            ops.append(dist.P2POp(dist.irecv, hi_halo, self.rank + 1, self.group))
+        if self.has_lower:
+            ops.append(dist.P2POp(dist.isend, first, self.rank - 1, self.group))
+            ops.append(dist.P2POp(dist.irecv, lo_halo, self.rank - 1, self.group))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+    # ---- the grow
+    def grow(self, threshold):
+        """enqueue label -> exchange -> resolve -> output; returns the slab's mask tensor"""
+        lib, st, plane = self.lib, self._stream(), self.nx * self.ny
+        slab_ptr = self.buf.data_ptr() + plane
+        self._ck(lib.rg_slab_label(self.ctx, slab_ptr, self.nx, self.ny, self.nzl, int(self.has_lower), int(self.has_upper),
+                                   self.seeds_dev.data_ptr() if self.nseeds else None, self.nseeds, int(threshold),
+                                   self.mask.data_ptr(), st), "rg_slab_label")
+        if self.world > 1:
+            torch, dist = self.torch, self.dist
+            self.counts.zero_()
+            if self.has_lower:
+                self._ck(lib.rg_slab_export(self.ctx, 0, self.lists[0].data_ptr(), self.counts.data_ptr(), st), "rg_slab_export")
+            if self.has_upper:
+                self._ck(lib.rg_slab_export(self.ctx, 1, self.lists[1].data_ptr(), self.counts.data_ptr(), st), "rg_slab_export")
+            if not (self.has_lower or self.has_upper):
+                raise RuntimeError("unreachable")
+            dist.all_gather_into_tensor(self.all_counts, self.counts, group=self.group)
+            cnt = self.all_counts.cpu().numpy().astype(np.int64).reshape(self.world, 4)          # the one host sync of the exchange
+            for r in range(self.world - 1):
+                if cnt[r, 1] != cnt[r + 1, 0]:
+                    raise RuntimeError(f"interface {r}/{r + 1}: list lengths differ ({cnt[r, 1]} vs {cnt[r + 1, 0]})")
+            maxn = int(max(cnt[:, 0].max(), cnt[:, 1].max()))
+            if maxn > 0:
+                mine = self.lists[:, :maxn].contiguous()
+                flat = torch.empty(self.world * 2 * maxn, dtype=torch.int32, device=self.device)
+                dist.all_gather_into_tensor(flat, mine.view(-1), group=self.group)
+                gathered = flat.view(self.world, 2, maxn)
+                off = np.ones(self.world + 1, np.int64)
+                off[1:] = 1 + np.cumsum(cnt[:, 2])
+                xpar = torch.empty(int(off[-1]) + 1, dtype=torch.int32, device=self.device)
+                for r in range(self.world):
+                    for side in (0, 1):
+                        n = int(cnt[r, side])
+                        if n:
+                            self._ck(lib.rg_slab_resolve_init(self.ctx, xpar.data_ptr(), gathered[r, side].data_ptr(), n,
+                                                              int(off[r]), st), "rg_slab_resolve_init")
+                for r in range(self.world - 1):
+                    n = int(cnt[r, 1])
+                    if n:
+                        self._ck(lib.rg_slab_resolve_union(self.ctx, xpar.data_ptr(), gathered[r, 1].data_ptr(), int(off[r]),
+                                                           gathered[r + 1, 0].data_ptr(), int(off[r + 1]), n, st),
+                                 "rg_slab_resolve_union")
+                for side in (0, 1):
+                    n = int(cnt[self.rank, side])
+                    if n:
+                        self._ck(lib.rg_slab_resolve_apply(self.ctx, xpar.data_ptr(), gathered[self.rank, side].data_ptr(), n,
+                                                           int(off[self.rank]), st), "rg_slab_resolve_apply")
+                self._keepalive = (gathered, xpar, mine)
+            self.rounds = 1
+        self._ck(lib.rg_slab_finish(self.ctx, st), "rg_slab_finish")
+        return self.mask

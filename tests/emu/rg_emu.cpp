@@ -186,3 +186,55 @@ extern "C" int emu_grow_slabs(int cfg, int G, const uint8_t *image, int64_t nx, 
     if (cfg == 1) return emu_grow_slabs_t<CfgS3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
     return emu_grow_slabs_t<CfgT3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
 }
+
+/* ---- the slab phases of include/rg.h on HOST memory, same names and signatures, so that the
+ * `not gpu` tests can drive rgb200.SlabGrower over the gloo backend with CPU tensors.  TEST ONLY. ---- */
+static int g_cfg = 1;
+extern "C" void emu_set_cfg(int cfg) { g_cfg = cfg; }
+struct EmuCtx { EmuState E; bool have; int cfg; std::vector<int32_t> seeds; };
+
+#define DISPATCH(cfg, CALL) do { if ((cfg) == 0) { typedef Cfg3D C; CALL; } else if ((cfg) == 1) { typedef CfgS3 C; CALL; } else { typedef CfgT3 C; CALL; } } while (0)
+
+extern "C" int rg_ctx_create(int, void **out) { *out = new EmuCtx(); ((EmuCtx *)*out)->have = false; return 0; }
+extern "C" void rg_ctx_destroy(void *c) { delete (EmuCtx *)c; }
+extern "C" const char *rg_last_error(void) { return "emulator"; }
+extern "C" int rg_slab_label(void *cv, const uint8_t *slab, int64_t nx, int64_t ny, int64_t nzl, int has_lower, int has_upper,
+                             const int32_t *seeds, int nseeds, int T, uint8_t *mask, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; c->cfg = g_cfg;
+    c->seeds.assign(seeds, seeds + 3 * (size_t)nseeds);
+    DISPATCH(c->cfg, (emu_setup<C>(c->E, slab, nx, ny, nzl, has_lower, has_upper, c->seeds.data(), nseeds, T, mask), emu_label<C>(c->E)));
+    c->have = true;
+    return 0;
+}
+extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny)
+{
+    int64_t r = 0;
+    DISPATCH(g_cfg, (r = ((nx + C::TX - 1) / C::TX) * ((ny + C::TY - 1) / C::TY) * (int64_t)C::FZN));
+    return r;
+}
+extern "C" int rg_slab_export(void *cv, int side, uint32_t *roots, uint32_t *counts3, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; HostExec ex;
+    DISPATCH(c->cfg, (export_interface<C>(ex, c->E.P, side, roots, counts3 + side)));
+    counts3[2] = c->E.counters[CTR_NODES];
+    return 0;
+}
+extern "C" int rg_slab_resolve_init(void *, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off, void *)
+{
+    HostExec ex; xpar[0] = 0; resolve_init(ex, xpar, roots, n, off); return 0;
+}
+extern "C" int rg_slab_resolve_union(void *, uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint32_t *b, uint32_t offb, uint32_t n, void *)
+{
+    HostExec ex; resolve_union(ex, xpar, a, offa, b, offb, n); return 0;
+}
+extern "C" int rg_slab_resolve_apply(void *cv, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; HostExec ex; resolve_apply(ex, c->E.P, xpar, roots, n, off); return 0;
+}
+extern "C" int rg_slab_finish(void *cv, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv;
+    DISPATCH(c->cfg, (emu_finish<C>(c->E)));
+    return c->E.counters[CTR_STATUS] ? -4 : 0;
+}

@@ -1,0 +1,294 @@
+"""Parity of the CUDA engine with the oracle, through the C ABI (libb200rg.so).  Needs a B200.
+
+Bit-exact everywhere (integer/byte path).  Sizes the oracle finishes in seconds are compared byte
+for byte; the full-size configurations of BASELINE.json are checked through size-independent
+properties (analytic region sizes, idempotence, slab-count independence)."""
+import ctypes, hashlib
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rg():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.fail("the -m gpu tests need a CUDA device; the engine has no CPU path")
+    import rgb200
+    rgb200.load_library()
+    return rgb200
+
+
+@pytest.fixture(scope="module")
+def ctx(rg):
+    c = rg.Context(0)
+    yield c
+    c.close()
+
+
+def dev_grow(rg, ctx, img, seeds, T):
+    import torch
+    d_img = torch.from_numpy(np.ascontiguousarray(img)).cuda()
+    s = np.ascontiguousarray(np.asarray(seeds, np.int32).reshape(-1, 3))
+    d_seeds = torch.from_numpy(s).cuda() if len(s) else None
+    out = torch.full_like(d_img, 9)
+    ctx.grow(d_img, d_seeds, T, out)
+    torch.cuda.synchronize()
+    st = ctx.status()
+    assert st["status"] == 0
+    return out.cpu().numpy()
+
+
+# ---------------------------------------------------------------- reference fixtures (C0, C1)
+@pytest.mark.parametrize("k", [1, 2, 3, 4])
+def test_region_c_pictures(rg, oracle, golden, k):
+    """rg_grow_region_2d == unmodified region.c (4 corner seeds, |d|<2) incl. write_image's masking"""
+    img = golden["arrays"][f"pic{k}"]
+    mask, out = rg.grow_region_2d(img, apply=True)
+    assert set(np.unique(mask)) <= {0, 1}
+    assert hashlib.sha256(out.tobytes()).hexdigest() == golden["pics"][f"pic{k}"]["out_sha256"]
+    assert (mask == oracle.grow(img, oracle.seeds_2d(512, 512), 2)).all()
+    mask2, img2 = rg.grow_region_2d(img, apply=False)
+    assert (mask2 == mask).all() and (img2 == img).all()
+
+
+def test_c0_single_seed(rg, oracle, golden):
+    img = golden["arrays"]["pic1"]
+    m = rg.grow(img, [[4, 4, 0]], 2)
+    assert int(m.sum()) == 24056 and (m == oracle.grow(img, [[4, 4, 0]], 2)).all()
+
+
+def test_c1_reference_volume_all_three_names(rg, oracle, golden):
+    """grow_region_gpu / grow_region_gpu_shared / grow_region_serial on the reference's own 512^3 volume"""
+    vol = oracle.create_data_ref()
+    assert oracle.fnv(vol) == golden["c1"]["volume_fnv1a64"]
+    m = rg.grow_region_gpu_shared(vol)
+    assert int(m.sum()) == 2197899
+    assert oracle.fnv(m) == golden["c1"]["mask_fnv1a64"]
+    assert set(np.unique(m)) == {0, 1}                         # never a 2 (raycast.cu:689-692 can leave them)
+    assert (rg.grow_region_gpu(vol) == m).all()
+    assert (rg._grow_512("grow_region_serial", vol) == m).all()
+
+
+# ---------------------------------------------------------------- random grids, ragged sizes, edge cases
+SHAPES3 = [(1, 1, 1), (3, 5, 7), (17, 33, 65), (16, 32, 64), (33, 65, 130), (40, 31, 200), (2, 40, 129), (70, 9, 16), (5, 100, 48)]
+
+
+@pytest.mark.parametrize("shape", SHAPES3)
+@pytest.mark.parametrize("levels,T", [(3, 1), (7, 2), (2, 1)])
+def test_random_volumes(rg, ctx, oracle, shape, levels, T):
+    rng = np.random.default_rng(abs(hash((shape, levels, T))) % 2**32)
+    img = rng.integers(0, levels, size=shape, dtype=np.uint8)
+    nz, ny, nx = shape
+    seeds = np.stack([rng.integers(-1, nx + 1, 8), rng.integers(-1, ny + 1, 8), rng.integers(-1, nz + 1, 8)], 1)
+    seeds[0] = 0
+    want = oracle.grow(img, seeds, T)
+    assert (dev_grow(rg, ctx, img, seeds, T) == want).all()
+    assert (rg.grow(img, seeds, T) == want).all()              # host-pointer entry point
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (7, 5), (300, 200), (256, 128), (257, 129), (513, 700), (31, 1000), (1000, 17)])
+@pytest.mark.parametrize("levels,T", [(3, 1), (9, 2)])
+def test_random_images(rg, ctx, oracle, shape, levels, T):
+    rng = np.random.default_rng(abs(hash((shape, levels, T))) % 2**32)
+    img = rng.integers(0, levels, size=shape, dtype=np.uint8)
+    ny, nx = shape
+    seeds = np.stack([rng.integers(-1, nx + 1, 8), rng.integers(-1, ny + 1, 8), np.zeros(8, np.int64)], 1)
+    seeds[0] = 0
+    assert (dev_grow(rg, ctx, img, seeds, T) == oracle.grow(img, seeds, T)).all()
+
+
+@pytest.mark.parametrize("T", [-5, 0, 1, 2, 128, 255, 256, 1000])
+def test_threshold_range(rg, ctx, oracle, T):
+    rng = np.random.default_rng(1000 + T)
+    img = rng.integers(0, 256, size=(20, 40, 96), dtype=np.uint8)
+    seeds = [[0, 0, 0], [95, 39, 19], [50, 20, 10]]
+    assert (dev_grow(rg, ctx, img, seeds, T) == oracle.grow(img, seeds, T)).all()
+
+
+def test_seed_edge_cases(rg, ctx, oracle):
+    img = np.zeros((20, 40, 96), np.uint8); img[:, :, 48] = 9   # a wall splits the volume
+    assert not dev_grow(rg, ctx, img, np.zeros((0, 3), np.int32), 1).any()          # no seeds
+    assert not dev_grow(rg, ctx, img, [[-1, 0, 0], [96, 0, 0], [0, 40, 0], [0, 0, 20]], 1).any()   # all out of range
+    dup = [[3, 3, 3]] * 5 + [[95, 39, 19]]                                              # duplicates, both halves
+    got = dev_grow(rg, ctx, img, dup, 1)
+    assert (got == oracle.grow(img, dup, 1)).all() and got.sum() == 20 * 40 * 95
+    wall = dev_grow(rg, ctx, img, [[48, 0, 0]], 1)
+    assert wall.sum() == 20 * 40 and wall[:, :, 48].all()
+
+
+def test_many_seeds_radix_sort_path(rg, ctx, oracle):
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 4, size=(40, 70, 130), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 130, 5000), rng.integers(0, 70, 5000), rng.integers(0, 40, 5000)], 1)
+    assert (dev_grow(rg, ctx, img, seeds, 1) == oracle.grow(img, seeds, 1)).all()
+
+
+def test_all_similar_and_none_similar(rg, ctx, oracle):
+    img = np.full((33, 65, 130), 7, np.uint8)
+    assert dev_grow(rg, ctx, img, [[129, 64, 32]], 1).all()
+    chk = (np.indices((33, 65, 130)).sum(0) % 2 * 50).astype(np.uint8)              # checkerboard: no edges at T<=50
+    got = dev_grow(rg, ctx, chk, [[5, 5, 5], [0, 0, 0]], 50)
+    assert got.sum() == 2 and got[5, 5, 5] == 1 and got[0, 0, 0] == 1
+
+
+def test_tile_face_corridors(rg, ctx, oracle):
+    """1-voxel corridors that cross tile faces, edges and corners of the 64x32x16 tiling"""
+    img = np.zeros((48, 96, 192), np.uint8)
+    path = np.zeros_like(img, bool)
+    path[15, 31, :] = True; path[15:18, 31, 191] = True; path[17, 31:65, 191] = True     # along x, then z, then y
+    path[17, 64, 60:192] = True; path[16:48, 64, 63] = True; path[47, 30:65, 63] = True
+    path[0:48, 32, 64] = True
+    img[path] = 100
+    seeds = [[0, 31, 15]]
+    got = dev_grow(rg, ctx, img, seeds, 1)
+    assert (got == oracle.grow(img, seeds, 1)).all()
+    assert got.sum() > 400
+
+
+# ---------------------------------------------------------------- synthetic generators and benchmark shapes
+@pytest.mark.parametrize("kind,name,n", [(1, "c1h", 96), (2, "c2", 320), (3, "c3", 80), (4, "c4", 128), (3, "c3", 33), (1, "c1h", 50)])
+def test_device_generators_match_cpu_definitions(rg, ctx, oracle, kind, name, n):
+    import torch
+    want, seeds, T = oracle.synth(name, n, 0x5EED0000 + kind)
+    out = torch.empty(want.shape, dtype=torch.uint8, device="cuda")
+    ctx.synth(kind, out, n, 0x5EED0000 + kind)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == want).all()
+    assert (rg.synth_seeds(kind, n, 0x5EED0000 + kind) == seeds).all()
+    assert (dev_grow(rg, ctx, want, seeds, T) == oracle.grow(want, seeds, T)).all()
+
+
+@pytest.mark.parametrize("kind,name,n", [(1, "c1h", 256), (3, "c3", 192), (4, "c4", 256), (2, "c2", 4096)])
+def test_benchmark_shapes_mid_size(rg, ctx, oracle, kind, name, n):
+    img, seeds, T = oracle.synth(name, n, 0x5EED0000 + kind)
+    assert (dev_grow(rg, ctx, img, seeds, T) == oracle.grow(img, seeds, T)).all()
+
+
+def test_c3_full_size_properties(rg, ctx, oracle):
+    """C3 at BASELINE.json's full size (1024^3): region size is known in closed form; the mask equals
+    'voxel is corridor'; growing the mask itself (T=1) from the same seed is idempotent."""
+    import torch
+    n = 1024
+    img = torch.empty((n, n, n), dtype=torch.uint8, device="cuda")
+    ctx.synth(3, img, n)
+    seeds = torch.tensor([[0, 0, 0]], dtype=torch.int32, device="cuda")
+    out = torch.empty_like(img)
+    ctx.grow(img, seeds, 1, out)
+    torch.cuda.synchronize()
+    assert ctx.status()["status"] == 0
+    assert int(out.sum(dtype=torch.int64)) == oracle.lib.oracle_c3_count(n)
+    assert bool(((img == 200) == (out == 1)).all())
+    out2 = torch.empty_like(img)
+    ctx.grow(out, seeds, 1, out2)                                   # mask as an image: region = its 1-component of the seed
+    torch.cuda.synchronize()
+    assert bool((out2 == out).all())
+    # a far-away seed reaches the same single region
+    seeds2 = torch.tensor([[n - 2, n - 2, n - 2]], dtype=torch.int32, device="cuda")
+    ctx.grow(img, seeds2, 1, out2)
+    torch.cuda.synchronize()
+    assert bool((out2 == out).all())
+
+
+def test_c2_full_size_properties(rg, ctx, oracle):
+    """C2 at full size (16384^2, 64 seeds): every solid's area is counted on the device and compared with
+    the mask restricted to solids; noise seeds contribute nothing outside; sub-image parity vs oracle."""
+    import torch
+    n = 16384
+    img = torch.empty((n, n), dtype=torch.uint8, device="cuda")
+    ctx.synth(2, img, n, 0x5EED0002)
+    seeds_np = rg.synth_seeds(2, n, 0x5EED0002)
+    seeds = torch.from_numpy(seeds_np).cuda()
+    out = torch.empty_like(img)
+    ctx.grow(img, seeds, 2, out)
+    torch.cuda.synchronize()
+    assert ctx.status()["status"] == 0
+    assert bool(((img >= 40) == (out == 1)).all())                  # all 64 solids hold a seed; noise (<20) never joins
+    # first cell row x first two cells against the oracle (the bar across cells + its noise surroundings)
+    sub = img[:2048, :4096].cpu().numpy()
+    sub_seeds = [s for s in seeds_np.tolist() if s[0] < 4096 and s[1] < 2048]
+    assert (oracle.grow(sub, sub_seeds, 2) == out[:2048, :4096].cpu().numpy()).all()
+
+
+# ---------------------------------------------------------------- z-slab path on one device ("fake cluster")
+def slab_grow_one_device(rg, img, seeds, T, G):
+    """run the multi-rank protocol for G logical ranks on one GPU by calling the C ABI phases in turn"""
+    import torch
+    lib = rg.load_library()
+    nz, ny, nx = img.shape
+    plane = nx * ny
+    ranks = []
+    for r in range(G):
+        z0, z1 = rg.slab_bounds(nz, r, G)
+        h = ctypes.c_void_p(); assert lib.rg_ctx_create(0, ctypes.byref(h)) == 0
+        buf = torch.zeros((z1 - z0 + 2) * plane, dtype=torch.uint8, device="cuda")
+        lo, hi = max(z0 - 1, 0), min(z1 + 1, nz)
+        buf[(lo - z0 + 1) * plane:(hi - z0 + 1) * plane] = torch.from_numpy(img[lo:hi].reshape(-1)).cuda()
+        mask = torch.empty((z1 - z0) * plane, dtype=torch.uint8, device="cuda")
+        s = np.asarray([[x, y, z - z0] for x, y, z in np.asarray(seeds).reshape(-1, 3).tolist() if z0 <= z < z1], np.int32).reshape(-1, 3)
+        d_s = torch.from_numpy(s).cuda() if len(s) else None
+        cap = int(lib.rg_slab_interface_capacity(nx, ny))
+        lists = torch.zeros((2, cap), dtype=torch.int32, device="cuda")
+        counts = torch.zeros(4, dtype=torch.int32, device="cuda")
+        assert lib.rg_slab_label(h, buf.data_ptr() + plane, nx, ny, z1 - z0, int(r > 0), int(r < G - 1),
+                                 d_s.data_ptr() if d_s is not None else None, len(s), T, mask.data_ptr(), None) == 0
+        if r > 0:
+            assert lib.rg_slab_export(h, 0, lists[0].data_ptr(), counts.data_ptr(), None) == 0
+        if r < G - 1:
+            assert lib.rg_slab_export(h, 1, lists[1].data_ptr(), counts.data_ptr(), None) == 0
+        ranks.append(dict(h=h, buf=buf, mask=mask, lists=lists, counts=counts, z0=z0, z1=z1, seeds=d_s))
+    torch.cuda.synchronize()
+    cnt = np.stack([rk["counts"].cpu().numpy() for rk in ranks]).astype(np.int64)
+    for r in range(G - 1):
+        assert cnt[r, 1] == cnt[r + 1, 0]
+    off = np.ones(G + 1, np.int64); off[1:] = 1 + np.cumsum(cnt[:, 2])
+    for me in range(G):                                             # every rank resolves redundantly
+        xpar = torch.empty(int(off[-1]) + 1, dtype=torch.int32, device="cuda")
+        h = ranks[me]["h"]
+        for r in range(G):
+            for side in (0, 1):
+                if cnt[r, side]:
+                    assert lib.rg_slab_resolve_init(h, xpar.data_ptr(), ranks[r]["lists"][side].data_ptr(), int(cnt[r, side]), int(off[r]), None) == 0
+        for r in range(G - 1):
+            if cnt[r, 1]:
+                assert lib.rg_slab_resolve_union(h, xpar.data_ptr(), ranks[r]["lists"][1].data_ptr(), int(off[r]),
+                                                 ranks[r + 1]["lists"][0].data_ptr(), int(off[r + 1]), int(cnt[r, 1]), None) == 0
+        for side in (0, 1):
+            if cnt[me, side]:
+                assert lib.rg_slab_resolve_apply(h, xpar.data_ptr(), ranks[me]["lists"][side].data_ptr(), int(cnt[me, side]), int(off[me]), None) == 0
+        assert lib.rg_slab_finish(h, None) == 0
+        torch.cuda.synchronize()
+    out = np.concatenate([rk["mask"].cpu().numpy() for rk in ranks]).reshape(img.shape)
+    for rk in ranks:
+        st = (ctypes.c_uint32 * 4)()
+        assert lib.rg_ctx_status(rk["h"], st) == 0
+        lib.rg_ctx_destroy(rk["h"])
+    return out
+
+
+@pytest.mark.parametrize("G", [2, 4, 8])
+def test_slabs_equal_single(rg, ctx, oracle, G):
+    img, seeds, T = oracle.synth("c4", 128, 0x5EED0004)             # z-serpentine: 64 crossings per interface
+    want = oracle.grow(img, seeds, T)
+    assert (slab_grow_one_device(rg, img, seeds, T, G) == want).all()
+
+
+@pytest.mark.parametrize("G", [2, 3, 5])
+def test_slabs_random_ragged(rg, ctx, oracle, G):
+    rng = np.random.default_rng(40 + G)
+    img = rng.integers(0, 3, size=(37, 45, 150), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 150, 6), rng.integers(0, 45, 6), rng.integers(0, 37, 6)], 1)
+    assert (slab_grow_one_device(rg, img, seeds, 1, G) == oracle.grow(img, seeds, 1)).all()
+
+
+def test_apply_mask_device(rg, ctx, oracle, golden):
+    import torch
+    img = golden["arrays"]["pic3"]
+    d = torch.from_numpy(img.copy()).cuda()
+    seeds = torch.from_numpy(oracle.seeds_2d(512, 512)).cuda()
+    m = torch.empty_like(d)
+    ctx.grow(d, seeds, 2, m)
+    ctx.apply_mask(d, m)
+    torch.cuda.synchronize()
+    assert hashlib.sha256(d.cpu().numpy().tobytes()).hexdigest() == golden["pics"]["pic3"]["out_sha256"]

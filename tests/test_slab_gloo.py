@@ -1,0 +1,77 @@
+"""The multi-rank host protocol (rgb200.SlabGrower) on CPU: world_size 2 and 3, gloo backend, CPU
+tensors, with the sequential emulator (tests/emu, test code) standing in for the CUDA library
+behind the very same C signatures.  Checks partitioning, the static image-halo swap, the
+all-gather of interface lists and the redundant resolve against the oracle."""
+import ctypes, os, subprocess, sys
+import numpy as np
+import pytest
+import torch
+import torch.multiprocessing as mp
+from conftest import ROOT, PKG
+
+SLAB_FNS = ["rg_ctx_create", "rg_ctx_destroy", "rg_last_error", "rg_slab_label", "rg_slab_interface_capacity",
+            "rg_slab_export", "rg_slab_resolve_init", "rg_slab_resolve_union", "rg_slab_resolve_apply", "rg_slab_finish"]
+
+
+def _worker(rank, world, port, img, seeds, T, cfg, out_q):
+    import torch.distributed as dist
+    sys.path.insert(0, PKG)
+    import rgb200
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        lib = ctypes.CDLL(os.path.join(ROOT, "tests", "emu", "librg_emu.so"))
+        rgb200.bind(lib, SLAB_FNS)
+        lib.emu_set_cfg(cfg)
+        h = ctypes.c_void_p(); lib.rg_ctx_create(0, ctypes.byref(h))
+        nz, ny, nx = img.shape
+        g = rgb200.SlabGrower(lib, h, nx, ny, nz, rank, world, torch.device("cpu"), use_cuda_stream=False)
+        g.image.copy_(torch.from_numpy(img[g.z0:g.z1]))
+        g.exchange_image_halos()
+        g.set_seeds(seeds)
+        m = g.grow(T)
+        out_q.put((rank, g.z0, g.z1, m.numpy().copy()))
+        dist.barrier()
+    except Exception as e:                                  # surface the failure instead of a queue timeout
+        out_q.put((rank, -1, -1, repr(e)))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+def run_world(world, img, seeds, T, cfg, port):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_worker, args=(r, world, port, img, seeds, T, cfg, q)) for r in range(world)]
+    for p in ps:
+        p.start()
+    parts = [q.get(timeout=120) for _ in range(world)]
+    for r, z0, _, m in parts:
+        assert z0 >= 0, f"rank {r}: {m}"
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    out = np.zeros(img.shape, np.uint8)
+    for _, z0, z1, m in parts:
+        out[z0:z1] = m
+    return out
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "emu")])
+
+
+@pytest.mark.parametrize("world,cfg,port", [(2, 1, 29611), (3, 2, 29612)])
+def test_slab_grower_gloo(oracle, world, cfg, port):
+    img, seeds, T = oracle.synth("c4", 64, 0x5EED0004)         # z-serpentine crosses every interface 64 times
+    got = run_world(world, img, seeds, T, cfg, port)
+    assert (got == oracle.grow(img, seeds, T)).all()
+
+
+def test_slab_grower_gloo_random(oracle):
+    rng = np.random.default_rng(77)
+    img = rng.integers(0, 3, size=(21, 10, 70), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 70, 6), rng.integers(0, 10, 6), rng.integers(0, 21, 6)], 1).astype(np.int32)
+    got = run_world(2, img, seeds, 1, 1, 29613)
+    assert (got == oracle.grow(img, seeds, 1)).all()
