@@ -311,7 +311,7 @@ def main():
         if sampler:
             res["clocks"] = sampler.stop()
         st = ctx.status()
-        res.update(ms_per_step=ms, value=nvox / (ms * 1e-3) / 1e9, nvox=nvox, launches=launches, nodes=st["nodes"], status=st["status"])
+        res.update(ms_per_step=ms, value=nvox / (ms * 1e-3) / 1e9, nvox=nvox, launches=launches, nodes=st["nodes"], status=st["status"], complex_tiles=st["complex_tiles"], region_tiles=st["region_tiles"])
         # per-kernel CUDA-event times (separate short loop, profiling events on the same stream)
         ctx.profile(True)
         acc = {}
@@ -331,7 +331,8 @@ def main():
             L = load_oracle(); L.oracle_c3_count.restype = ctypes.c_int64; L.oracle_c3_count.argtypes = [ctypes.c_int64]
             res["check"] = "ok" if cnt == L.oracle_c3_count(n) else f"MISMATCH expected {L.oracle_c3_count(n)}"
         else:
-            solid = int((img >= 30).sum(dtype=torch.int64)); inside = int(((img >= 30) & (out == 1)).sum(dtype=torch.int64))
+            sel = (img == 35) if kind == 1 else (img >= 30)          # C1: one seed, in the box of value 35 (raycast.cu:140-142)
+            solid = int(sel.sum(dtype=torch.int64)); inside = int((sel & (out == 1)).sum(dtype=torch.int64))
             if dist is not None:
                 t = torch.tensor([solid, inside], dtype=torch.int64, device=dev); dist.all_reduce(t); solid, inside = (int(v) for v in t.tolist())
             ok = inside == solid and 0 <= cnt - solid < 100000
@@ -356,7 +357,9 @@ def main():
         "config": {"workload": main_res["workload"], "n": n, "seeds": main_res["nseeds"], "threshold": main_res["threshold"],
                    "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (no flush needed)" if main_res["nvox"] > 4e8 else "input+output ~2x L2; no flush",
-                   "check": main_res["check"], "region_voxels": main_res["region_voxels"], "coarse_nodes": main_res["nodes"]},
+                   "check": main_res["check"], "region_voxels": main_res["region_voxels"], "coarse_nodes": main_res["nodes"],
+                   "tiles": {"total": -(-n // 64) * -(-n // 32) * -(-n // 16) if WORKLOADS[wl][2] == 3 else -(-n // 128) * -(-n // 254),
+                             "full_label_pass": main_res["complex_tiles"], "with_region": main_res["region_tiles"]}},
         "gpu_launches": main_res["launches"] * args.steps,
         "clocks": main_res.get("clocks"),
         "roofline": {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -379,7 +382,7 @@ def main():
                 try:
                     r = run(o, WORKLOADS[o][1], max(3, min(args.steps, 5)), 3)
                     r["path_frac"] = ALGO_BYTES_PER_VOXEL * r["nvox"] / (r["ms_per_step"] * 1e-3) / 1e9 / peak
-                    others[o] = {k: r[k] for k in ("workload", "value", "ms_per_step", "kernel_ms", "check", "region_voxels", "path_frac")}
+                    others[o] = {k: r[k] for k in ("workload", "value", "ms_per_step", "kernel_ms", "check", "region_voxels", "path_frac", "complex_tiles", "region_tiles")}
                 except Exception as e:
                     others[o] = {"error": repr(e)}
             line["other_workloads"] = others

@@ -78,7 +78,7 @@ int rg_grow_device(rg_ctx *ctx, const uint8_t *d_image, int64_t nx, int64_t ny, 
                    const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream);
 
 /* Synchronises the stream last used and returns RG_OK or RG_ERR_INTERNAL / RG_ERR_CUDA;
- * stats (may be NULL) receives {nodes, status bits, mismatching faces, 0}. */
+ * stats (may be NULL) receives {coarse nodes, status bits, tiles labelled by the full pass, tiles holding region voxels}. */
 int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);
 
 /* Optional per-kernel timing with CUDA events on the launching stream (used by bench.py for the

@@ -30,7 +30,7 @@
 namespace rg {
 
 enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
-enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_MAXNODES = 3, CTR_WORDS = 8 };
+enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_WORDS = 8 };
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
 template <int TX_, int TY_, int TZ_>
@@ -41,7 +41,16 @@ struct TileCfg {
     static constexpr int NV = TX * TY * TZ;        /* voxels per tile */
     static constexpr int HZ = TZ > 1 ? 1 : 0;      /* z halo planes (none for images) */
     static constexpr int PZ = TZ + 2 * HZ, PY = TY + 2;
-    static constexpr int CX = TX / 16;             /* 16-byte chunks per row */
+    static constexpr int CX = TX / 16;             /* 16-byte chunks per row (own voxels) */
+    static constexpr int XO = 16;                  /* staged rows start 16 bytes left of the tile: x = -1 is byte 15 */
+    static constexpr int RS = TX + 32;             /* staged row stride: [x0-16, x0+TX+16) */
+    static constexpr int CXH = RS / 16;            /* 16-byte chunks per staged row */
+    static constexpr int PS = PY * RS;             /* staged plane stride */
+    static constexpr int IMG_BYTES = PZ * PS;
+    static constexpr int TMA_NY = PY <= 256 ? 1 : 2;   /* TMA boxes are at most 256 rows high */
+    static constexpr int BOXY = PY / TMA_NY;
+    static_assert(PY % TMA_NY == 0, "split rows evenly");
+    static_assert(TMA_NY == 1 || (BOXY * RS) % 128 == 0, "every TMA box must land 128-byte aligned");
     static constexpr int FXN = TY * TZ, FYN = TX * TZ, FZN = HZ ? TX * TY : 0;
     static constexpr int FXW = (FXN + 31) / 32, FYW = WX * TZ, FZW = HZ ? WX * TY : 0;
     static constexpr int FW_TOTAL = 2 * (FXW + FYW + FZW);
@@ -55,15 +64,16 @@ struct TileCfg {
     }
 };
 
-/* tile shapes: 32768 voxels either way */
+/* tile shapes: ~32 K voxels either way.  2-D: 254 rows so that the staged tile (256 rows) is one TMA box */
 typedef TileCfg<64, 32, 16> Cfg3D;
-typedef TileCfg<128, 256, 1> Cfg2D;
+typedef TileCfg<128, 254, 1> Cfg2D;
 
 struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint32_t node_base;          /* first global node id of this tile */
     uint32_t nnodes;
     uint16_t cnt[6];             /* face-list lengths, order XM XP YM YP ZM ZP */
-    uint16_t pad0, pad1;
+    uint16_t uniform;            /* 1: all voxels of the tile are one component (pass C needs no image read) */
+    uint16_t pad1;
     uint32_t pad2, pad3;
 };
 
@@ -76,6 +86,7 @@ struct Params {
     int32_t tmode;               /* 0: T <= 0 (no edges)  1: 1..255  2: T >= 256 (all edges) */
     uint32_t t4;                 /* T replicated into 4 bytes */
     int32_t fast16;              /* nx % 16 == 0 and both buffers 16-byte aligned */
+    int32_t use_tma;             /* tiles are staged by one cp.async.bulk.tensor (needs fast16) */
     const uint64_t *seed_keys;   /* sorted (tile << 16 | voxel-in-tile); ~0 = dropped */
     int32_t nseeds;
     TileRec *rec;
@@ -84,19 +95,20 @@ struct Params {
     uint16_t *nrep;              /* node -> root voxel index inside its tile */
     uint32_t *counters;          /* CTR_* */
     uint32_t node_cap;
+    uint32_t *complex_list;      /* tiles the fast labelling pass handed to the full one */
+    uint32_t *flag_list;         /* tiles that hold part of the region (pass C work list) */
 };
 
 /* ---------------------------------------------------------------- shared-memory tile state */
 template <class C>
-struct alignas(16) TileSmem {
-    union alignas(16) U {
+struct alignas(128) TileSmem {
+    union alignas(128) U {
         struct {
-            uint8_t img[C::PZ * C::PY * C::TX];    /* tile + y/z halo rows */
-            uint8_t xm[C::TY * C::TZ];             /* x = -1 column */
-            uint8_t xp[C::TY * C::TZ];             /* x = TX column */
+            uint8_t img[C::IMG_BYTES];             /* tile + 1-voxel halo, rows of RS bytes (see img_off) */
         } i;
         uint16_t parent[C::NV];                    /* run union-find (image is dead by then) */
     } u;
+    uint64_t mbar;                                 /* TMA completion barrier */
     uint32_t ex[C::NW], ey[C::NW], ez[C::NW];      /* bit i: voxel i similar to its +x/+y/+z neighbour (in-tile) */
     uint32_t fmask[C::FW_TOTAL];                   /* cross-tile edges per face, de-duplicated */
     uint16_t fprefix[C::FW_TOTAL + 2];
@@ -106,7 +118,7 @@ struct alignas(16) TileSmem {
     uint32_t scal[16];
     uint32_t scan_scratch[40];
 };
-enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6 };
+enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8 };
 
 /* ---------------------------------------------------------------- small helpers */
 RG_FN uint32_t valid_bits(int64_t n) { return n >= 32 ? 0xFFFFFFFFu : n <= 0 ? 0u : ((1u << n) - 1u); }
@@ -208,43 +220,41 @@ RG_FN void tile_origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz
     tz = (int)(r / (uint32_t)P.nty);
 }
 
-template <class C> RG_FN int img_off(int x, int y, int z) { return ((z + C::HZ) * C::PY + (y + 1)) * C::TX + x; }
+/* staged position of tile-local voxel (x,y,z), -1 <= x <= TX, -1 <= y <= TY, -HZ <= z <= TZ-1+HZ */
+template <class C> RG_FN int img_off(int x, int y, int z) { return ((z + C::HZ) * C::PY + (y + 1)) * C::RS + C::XO + x; }
 
 /* ---------------------------------------------------------------- stage a tile in shared memory */
 template <class C, class Exec>
-RG_FN void load_tile(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, int64_t y0, int64_t z0, bool halo)
+RG_FN void load_tile(Exec &ex, const Params &P, uint8_t *img, int64_t x0, int64_t y0, int64_t z0, bool halo)
 {
+    /* Generic staging (used when TMA is not available: unaligned rows, or the CPU walk of this code).
+       With 16-byte aligned rows every chunk is one asynchronous copy, so a thread keeps all its chunks
+       in flight; the caller runs ex.tile_wait() + a barrier before reading.  The TMA path of the CUDA
+       Exec (rg_engine.cu) produces the same bytes with one instruction per tile. */
     const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
     const int64_t zmin = -(int64_t)P.zlo_ext, zmax = nz + P.zhi_ext;          /* readable plane range */
-    ex.pfor(C::PZ * C::PY * C::CX, [&](int it) {
-        int c = it % C::CX, r = it / C::CX;
+    const bool fast = P.fast16 != 0;
+    ex.pfor(C::PZ * C::PY * C::CXH, [&](int it) {
+        int c = it % C::CXH, r = it / C::CXH;
         int py = r % C::PY, pz = r / C::PY;
         int ly = py - 1, lz = pz - C::HZ;
-        bool yh = (ly < 0 || ly >= C::TY), zh = (lz < 0 || lz >= C::TZ);
-        int64_t gx = x0 + 16 * c, gy = y0 + ly, gz = z0 + lz;
-        u32x4 v = {0, 0, 0, 0};
-        bool want = !(yh && zh) && (halo || !(yh || zh));
-        if (want && gy >= 0 && gy < ny && gz >= zmin && gz < zmax && gx < nx) {
-            const uint8_t *g = P.image + (gz * ny + gy) * nx + gx;
-            if (P.fast16) v = ld128_stream(g);
-            else {
-                uint32_t t[4] = {0, 0, 0, 0};
-                for (int b = 0; b < 16; b++) if (gx + b < nx) t[b >> 2] |= (uint32_t)g[b] << (8 * (b & 3));
-                v = u32x4{t[0], t[1], t[2], t[3]};
+        bool yh = (ly < 0 || ly >= C::TY), zh = (lz < 0 || lz >= C::TZ), xh = (c == 0 || c == C::CXH - 1);
+        bool want = !(yh && zh) && !(xh && (yh || zh)) && (halo || !(yh || zh || xh));
+        if (!want) return;                                      /* never read: edge / corner columns, halo of pass C */
+        int64_t gx = x0 - C::XO + 16 * c, gy = y0 + ly, gz = z0 + lz;
+        bool inside = gy >= 0 && gy < ny && gz >= zmin && gz < zmax && gx >= 0 && gx < nx;
+        if (xh) inside = inside && gz >= 0 && gz < nz;          /* x halo columns only matter for own rows */
+        uint8_t *dst = &img[(pz * C::PY + py) * C::RS + 16 * c];
+        if (fast) cp_async16(dst, P.image + (inside ? (gz * ny + gy) * nx + gx : 0), inside);
+        else {
+            uint32_t t[4] = {0, 0, 0, 0};
+            if (gy >= 0 && gy < ny && gz >= zmin && gz < zmax) {
+                const uint8_t *g = P.image + (gz * ny + gy) * nx;
+                for (int b = 0; b < 16; b++) if (gx + b >= 0 && gx + b < nx) t[b >> 2] |= (uint32_t)g[gx + b] << (8 * (b & 3));
             }
+            st128(dst, u32x4{t[0], t[1], t[2], t[3]});
         }
-        st128(&s.u.i.img[(pz * C::PY + py) * C::TX + 16 * c], v);
     });
-    if (halo) {
-        ex.pfor(2 * C::TY * C::TZ, [&](int it) {
-            int side = it / (C::TY * C::TZ), q = it % (C::TY * C::TZ);
-            int ly = q % C::TY, lz = q / C::TY;
-            int64_t gy = y0 + ly, gz = z0 + lz, gx = side ? x0 + C::TX : x0 - 1;
-            uint8_t v = 0;
-            if (gy < ny && gz < nz && gx >= 0 && gx < nx) v = P.image[(gz * ny + gy) * nx + gx];
-            (side ? s.u.i.xp : s.u.i.xm)[q] = v;
-        });
-    }
 }
 
 /* ---------------------------------------------------------------- edge bit planes (+ face masks if FACES) */
@@ -270,7 +280,7 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
             /* +x */
             uint32_t nextb = 0;
             if (wx < C::WX - 1) nextb = rowp[32];
-            else if (FACES) nextb = s.u.i.xp[z * C::TY + y];
+            else if (FACES) nextb = rowp[32];                        /* x = TX halo byte */
             shift8(a, nextb, b);
             uint32_t nextvalid = (gx0 + 32 < nx) ? 0x80000000u : 0u;
             uint32_t e = edge_word(a, b, tmode, t4) & vmask & ((vmask >> 1) | nextvalid);
@@ -280,27 +290,27 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
             }
             exw = e;
             if (FACES && wx == 0 && x0 > 0 && (vmask & 1u)) {
-                if (similar1(s.u.i.xm[z * C::TY + y], a[0] & 0xFFu, tmode, t4)) {
+                if (similar1(rowp[-1], a[0] & 0xFFu, tmode, t4)) {
                     int bi = z * C::TY + y; atomic_or(&s.fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31));
                 }
             }
             /* +y */
             if (y < vy - 1) {
-                load8(rowp + C::TX, b);
+                load8(rowp + C::RS, b);
                 eyw = edge_word(a, b, tmode, t4) & vmask;
             } else if (FACES && has_yp) {                       /* y == TY-1: edges into the +y tile */
-                load8(rowp + C::TX, b);
+                load8(rowp + C::RS, b);
                 uint32_t m = edge_word(a, b, tmode, t4) & vmask;
                 s.fmask[C::fw_off(F_YP) + z * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
             }
             if (FACES && y == 0 && has_ym) {
-                load8(rowp - C::TX, b);
+                load8(rowp - C::RS, b);
                 uint32_t m = edge_word(b, a, tmode, t4) & vmask;
                 s.fmask[C::fw_off(F_YM) + z * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
             }
             /* +z */
             if (C::HZ) {
-                const int zs = C::PY * C::TX;
+                const int zs = C::PS;
                 if (z < vz - 1) {
                     load8(rowp + zs, b);
                     ezw = edge_word(a, b, tmode, t4) & vmask;
@@ -354,6 +364,48 @@ RG_FN void label_runs(Exec &ex, TileSmem<C> &s)
     ex.sync();
 }
 
+/* ---------------------------------------------------------------- nodes, face lists and the tile record
+   (shared by the fast and the full labelling pass; S = TileSmem<C> or FastSmem<C>) */
+template <class C, class S, class Exec>
+RG_FN void emit_nodes(Exec &ex, const Params &P, uint32_t tile, S &s)
+{
+    /* dense node ids in root order */
+    uint32_t k = ex.scan16(C::NW, [&](int i) { return (uint32_t)popc(s.openbits[i]); }, s.wprefix, s.scan_scratch);
+    if (ex.tid() == 0) {
+        uint32_t base = k ? atomic_add(&P.counters[CTR_NODES], k) : 0u;
+        if (k && (base + k > P.node_cap || base + k < base)) { atomic_or(&P.counters[CTR_STATUS], ST_NODE_OVERFLOW); s.scal[SC_OVERFLOW] = 1; }
+        s.scal[SC_NODE_BASE] = base; s.scal[SC_NNODES] = k;
+    }
+    ex.sync();
+    const uint32_t base = s.scal[SC_NODE_BASE];
+    const bool ok = !s.scal[SC_OVERFLOW];
+    if (ok) {
+        ex.pfor(C::NW, [&](int wi) {
+            uint32_t m = s.openbits[wi];
+            if (!m) return;
+            uint32_t id = s.wprefix[wi], sb = s.seedbits[wi];
+            while (m) {
+                int b = ffs1(m) - 1; m &= m - 1;
+                uint32_t g = base + id++;
+                P.nparent[g] = ((sb >> b) & 1u) ? 0u : g;       /* seeded components start hooked to node 0 */
+                P.nrep[g] = (uint16_t)(wi * 32 + b);
+            }
+        });
+        uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
+        ex.pfor((int)s.scal[SC_ETOT], [&](int e) {
+            uint32_t r = s.ent_root[e];
+            ent[e] = (uint16_t)(s.wprefix[r >> 5] + popc(s.openbits[r >> 5] & ((1u << (r & 31)) - 1u)));
+        });
+    }
+    if (ex.tid() == 0) {
+        TileRec rc;
+        rc.node_base = base; rc.nnodes = ok ? k : 0u;
+        for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]) : (uint16_t)0;
+        rc.uniform = (uint16_t)(ok ? s.scal[SC_UNIFORM] : 0u); rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
+        P.rec[tile] = rc;
+    }
+}
+
 /* ================================================================ pass A */
 template <class C, class Exec>
 RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
@@ -371,9 +423,10 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
         while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < lo_key) lo = mid + 1; else hi = mid; }
         int a = lo; hi = P.nseeds;
         while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
-        s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0;
+        s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0; s.scal[SC_UNIFORM] = 0;
     }
-    load_tile<C>(ex, P, s, x0, y0, z0, true);
+    if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
+    ex.tile_wait(&s.mbar);
     ex.sync();
     build_edges<C, true>(ex, P, s, x0, y0, z0);
     ex.sync();
@@ -416,89 +469,63 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     }
     ex.sync();
 
-    /* dense node ids in root order */
-    uint32_t k = ex.scan16(C::NW, [&](int i) { return (uint32_t)popc(s.openbits[i]); }, s.wprefix, s.scan_scratch);
-    if (ex.tid() == 0) {
-        uint32_t base = k ? atomic_add(&P.counters[CTR_NODES], k) : 0u;
-        if (k && (base + k > P.node_cap || base + k < base)) { atomic_or(&P.counters[CTR_STATUS], ST_NODE_OVERFLOW); s.scal[SC_OVERFLOW] = 1; }
-        s.scal[SC_NODE_BASE] = base; s.scal[SC_NNODES] = k;
-    }
-    ex.sync();
-    const uint32_t base = s.scal[SC_NODE_BASE];
-    const bool ok = !s.scal[SC_OVERFLOW];
-    if (ok) {
-        ex.pfor(C::NW, [&](int wi) {
-            uint32_t m = s.openbits[wi];
-            if (!m) return;
-            uint32_t id = s.wprefix[wi], sb = s.seedbits[wi];
-            while (m) {
-                int b = ffs1(m) - 1; m &= m - 1;
-                uint32_t g = base + id++;
-                P.nparent[g] = ((sb >> b) & 1u) ? 0u : g;       /* seeded components start hooked to node 0 */
-                P.nrep[g] = (uint16_t)(wi * 32 + b);
-            }
-        });
-        uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
-        ex.pfor((int)s.scal[SC_ETOT], [&](int e) {
-            uint32_t r = s.ent_root[e];
-            ent[e] = (uint16_t)(s.wprefix[r >> 5] + popc(s.openbits[r >> 5] & ((1u << (r & 31)) - 1u)));
-        });
-    }
-    if (ex.tid() == 0) {
-        TileRec rc;
-        rc.node_base = base; rc.nnodes = ok ? k : 0u;
-        for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]) : (uint16_t)0;
-        rc.pad0 = rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
-        P.rec[tile] = rc;
-    }
+    emit_nodes<C>(ex, P, tile, s);
 }
 
 /* ================================================================ pass B: one (tile, +face) per item */
+enum { MERGE_LANES = 32 };     /* one warp per tile: lanes share the tile's three + face lists */
 template <class C, class Exec>
 RG_FN void merge_faces(Exec &ex, const Params &P)
 {
     const uint32_t ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
-    ex.gpfor((int64_t)ntiles * 3, [&](int64_t it) {
-        uint32_t tile = (uint32_t)(it / 3); int axis = (int)(it % 3);
+    ex.gpfor((int64_t)ntiles * MERGE_LANES, [&](int64_t it0) {
+        const uint32_t lane = (uint32_t)(it0 % MERGE_LANES);
+        const uint32_t tile = (uint32_t)(it0 / MERGE_LANES);
+        const TileRec ra = P.rec[tile];
+        if (!(ra.cnt[F_XP] | ra.cnt[F_YP] | ra.cnt[F_ZP])) return;
         int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
-        uint32_t nb;
-        if (axis == 0) { if (tx + 1 >= P.ntx) return; nb = tile + 1; }
-        else if (axis == 1) { if (ty + 1 >= P.nty) return; nb = tile + (uint32_t)P.ntx; }
-        else { if (tz + 1 >= P.ntz) return; nb = tile + (uint32_t)P.ntx * (uint32_t)P.nty; }
-        const TileRec &ra = P.rec[tile];
-        const int fa = 2 * axis + 1, fb = 2 * axis;
-        uint32_t cnt = ra.cnt[fa];
-        if (!cnt) return;
-        const TileRec &rb = P.rec[nb];
-        if (rb.cnt[fb] != cnt) { atomic_or(&P.counters[CTR_STATUS], ST_FACE_MISMATCH); atomic_add(&P.counters[CTR_FACE_MISMATCH], 1u); return; }
-        uint32_t offa = 0, offb = 0;
-        for (int f = 0; f < fa; f++) offa += ra.cnt[f];
-        for (int f = 0; f < fb; f++) offb += rb.cnt[f];
-        const uint16_t *ea = P.ent + (size_t)tile * C::ENT_MAX + offa;
-        const uint16_t *eb = P.ent + (size_t)nb * C::ENT_MAX + offb;
-        uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu;
-        for (uint32_t i = 0; i < cnt; i++) {
-            uint32_t a = ra.node_base + ea[i], b = rb.node_base + eb[i];
-            if (a == pa && b == pb) continue;
-            unite32(P.nparent, a, b);
-            pa = a; pb = b;
+        const uint16_t *ta = P.ent + (size_t)tile * C::ENT_MAX;
+        uint32_t offa = 0;
+        for (int axis = 0; axis < 3; axis++) {
+            const int fa = 2 * axis + 1, fb = 2 * axis;
+            offa += ra.cnt[fb];                                  /* skip this tile's own - face list */
+            const uint32_t cnt = ra.cnt[fa];
+            const uint32_t here = offa; offa += cnt;
+            if (!cnt) continue;
+            uint32_t nb;
+            if (axis == 0) { if (tx + 1 >= P.ntx) continue; nb = tile + 1; }
+            else if (axis == 1) { if (ty + 1 >= P.nty) continue; nb = tile + (uint32_t)P.ntx; }
+            else { if (tz + 1 >= P.ntz) continue; nb = tile + (uint32_t)P.ntx * (uint32_t)P.nty; }
+            const TileRec rb = P.rec[nb];
+            if (rb.cnt[fb] != cnt) {
+                if (lane == 0) { atomic_or(&P.counters[CTR_STATUS], ST_FACE_MISMATCH); atomic_add(&P.counters[CTR_FACE_MISMATCH], 1u); }
+                continue;
+            }
+            uint32_t offb = 0;
+            for (int f = 0; f < fb; f++) offb += rb.cnt[f];
+            const uint16_t *ea = ta + here;
+            const uint16_t *eb = P.ent + (size_t)nb * C::ENT_MAX + offb;
+            for (uint32_t i = lane; i < cnt; i += MERGE_LANES) unite32(P.nparent, ra.node_base + ea[i], rb.node_base + eb[i]);
         }
     });
 }
 
 /* ================================================================ pass C */
 template <class C, class Exec>
-RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0)
+RG_FN void fill_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0, uint32_t byte01)
 {
+    const uint32_t w = byte01 * 0x01010101u;
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
         int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
         int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
         if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
         uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
-        if (P.fast16) st128_stream(g, u32x4{0, 0, 0, 0});
-        else for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = 0;
+        if (P.fast16) st128_stream(g, u32x4{w, w, w, w});
+        else for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = (uint8_t)byte01;
     });
 }
+template <class C, class Exec>
+RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0) { fill_tile<C>(ex, P, x0, y0, z0, 0u); }
 
 template <class C, class Exec>
 RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
@@ -523,7 +550,8 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     ex.sync();
     if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
 
-    load_tile<C>(ex, P, s, x0, y0, z0, false);
+    if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, false);
+    ex.tile_wait(&s.mbar);
     ex.sync();
     build_edges<C, false>(ex, P, s, x0, y0, z0);
     ex.sync();

@@ -6,6 +6,7 @@
  * entry points declared in include/rg.h.  There is deliberately no CPU path in this library.
  */
 #include <cuda_runtime.h>
+#include <cuda.h>                 /* CUtensorMap types only; the encoder is fetched with cudaGetDriverEntryPoint */
 #include <cub/device/device_radix_sort.cuh>
 #include <stdio.h>
 #include <stdlib.h>
@@ -13,13 +14,64 @@
 #include <mutex>
 
 #include "rg_core.h"
+#include "rg_fast.h"
 #include "rg_slab_core.h"
 #include "../../include/rg.h"
 
 using namespace rg;
 
 /* ------------------------------------------------------------------ Exec for a CUDA block */
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 struct DevExec {
+    const CUtensorMap *tmap = nullptr;      /* image descriptor (kernel parameter) */
+    uint32_t phase = 0;                     /* parity of the next mbarrier completion */
+    bool tma_pending = false;
+
+    /* one thread, once per kernel */
+    __device__ __forceinline__ void mbar_init(uint64_t *bar)
+    {
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(bar)) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
+    /* Stage the haloed tile [x0-16, x0+TX+16) x [y0-1, y0+TY+1) x [z0-1, z0+TZ+1) with the tensor-memory
+       accelerator: one elected thread, hardware zero-fill outside the volume, completion on the mbarrier. */
+    template <class C>
+    __device__ __forceinline__ bool tma_tile(const Params &P, uint8_t *img, uint64_t *bar, int64_t x0, int64_t y0, int64_t z0)
+    {
+        if (!P.use_tma) return false;
+        tma_pending = true;
+        if (threadIdx.x == 0) {
+            const uint32_t b = smem_u32(bar);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     /* earlier generic-proxy accesses to this buffer */
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(b), "r"((uint32_t)C::IMG_BYTES) : "memory");
+            const int cx = (int)x0 - C::XO, cz = (int)z0 - C::HZ + P.zlo_ext;
+#pragma unroll
+            for (int k = 0; k < C::TMA_NY; k++) {
+                const int cy = (int)y0 - 1 + k * C::BOXY;
+                asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                             :: "r"(smem_u32(img + k * C::BOXY * C::RS)), "l"((uint64_t)tmap), "r"(b), "r"(cx), "r"(cy), "r"(cz) : "memory");
+            }
+        }
+        return true;
+    }
+    __device__ __forceinline__ void tile_wait(uint64_t *bar)
+    {
+        cp_async_wait_all();
+        if (tma_pending) {
+            const uint32_t b = smem_u32(bar);
+            uint32_t done;
+            do {
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(b), "r"(phase) : "memory");
+            } while (!done);
+            phase ^= 1u;
+            tma_pending = false;
+        }
+    }
     __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
     template <class F> __device__ __forceinline__ void pfor(int n, F f)
     {
@@ -30,6 +82,9 @@ struct DevExec {
         for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) f(i);
     }
     __device__ __forceinline__ void sync() { __syncthreads(); }
+    __device__ __forceinline__ bool sync_or(bool p) { return __syncthreads_or(p ? 1 : 0) != 0; }
+    __device__ __forceinline__ uint32_t bid() const { return blockIdx.x; }
+    __device__ __forceinline__ uint32_t nblk() const { return gridDim.x; }
     /* block-wide exclusive scan of count(i), i < n, into out[i]; returns the total to every thread */
     template <class T, class F> __device__ __forceinline__ uint32_t scan(int n, F count, T *out, uint32_t *scratch)
     {
@@ -61,22 +116,50 @@ struct DevExec {
 };
 
 /* ------------------------------------------------------------------ kernels */
-#define RG_THREADS 512
+#define RG_THREADS 512          /* full tile passes: 2 CTAs/SM (105 KB smem each) */
+#define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (56 KB smem each) */
+#define RG_FLAG_THREADS 128     /* flag / zero-fill: no smem */
+#define RG_PERSISTENT_CTAS (148 * 2)
 
+/* pass A, fast path: every tile */
 template <class C>
-__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a(const Params P)
+__global__ void __launch_bounds__(RG_FAST_THREADS, 3) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    DevExec ex;
-    tile_pass_a<C>(ex, P, blockIdx.x, *reinterpret_cast<TileSmem<C> *>(smem_raw));
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    FastSmem<C> &s = *reinterpret_cast<FastSmem<C> *>(smem_raw);
+    DevExec ex; ex.tmap = &tmap;
+    if (P.use_tma) ex.mbar_init(&s.mbar);
+    tile_pass_a_fast<C>(ex, P, blockIdx.x, s);
 }
 
+/* pass A, full path: the tiles the fast path listed (persistent CTAs) */
 template <class C>
-__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P)
+__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a_full(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
+    DevExec ex; ex.tmap = &tmap;
+    if (P.use_tma) ex.mbar_init(&s.mbar);
+    pass_a_full_list<C>(ex, P, s);
+}
+
+/* pass C, part 1: zero-fill tiles without region voxels, list the others */
+template <class C>
+__global__ void __launch_bounds__(RG_FLAG_THREADS) k_flag_tiles(const Params P)
+{
     DevExec ex;
-    tile_pass_c<C>(ex, P, blockIdx.x, *reinterpret_cast<TileSmem<C> *>(smem_raw));
+    flag_tile<C>(ex, P, blockIdx.x);
+}
+
+/* pass C, part 2: the listed tiles (persistent CTAs) */
+template <class C>
+__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P, const __grid_constant__ CUtensorMap tmap)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
+    DevExec ex; ex.tmap = &tmap;
+    if (P.use_tma) ex.mbar_init(&s.mbar);
+    pass_c_list<C>(ex, P, s);
 }
 
 template <class C>
@@ -178,11 +261,45 @@ struct rg_ctx {
     bool attr_set;
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
+    CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     bool profile; cudaEvent_t ev[5]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
 };
 
+/* cuTensorMapEncodeTiled through the runtime, so the library does not link against libcuda */
+typedef CUresult (*tmap_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn get_tmap_encoder()
+{
+    static tmap_encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *p = nullptr; cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (tmap_encode_fn)p;
+        if (getenv("RG_NO_TMA")) fn = nullptr;              /* debugging aid: force the cp.async staging path */
+    }
+    return fn;
+}
+
+/* uint8 volume [nz_total][ny][nx] starting at `base`; box = one staged tile (TMA_NY boxes stacked in y) */
+template <class C>
+static bool make_tmap(CUtensorMap *tm, const uint8_t *base, int64_t nx, int64_t ny, int64_t nz_total)
+{
+    tmap_encode_fn enc = get_tmap_encoder();
+    if (!enc) return false;
+    cuuint64_t dims[3] = { (cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz_total };
+    cuuint64_t strides[2] = { (cuuint64_t)nx, (cuuint64_t)nx * (cuuint64_t)ny };
+    cuuint32_t box[3] = { (cuuint32_t)C::RS, (cuuint32_t)C::BOXY, (cuuint32_t)C::PZ };
+    cuuint32_t es[3] = { 1, 1, 1 };
+    if (strides[1] >= (1ull << 40)) return false;
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 struct Layout {
-    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, total;
+    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, total;
     uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
 };
 
@@ -214,6 +331,8 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
     L.off_cub = o; o = align_up(o + L.cub_bytes, 256);
     L.off_if0 = o; o = align_up(o + ((size_t)ntx * nty + 1) * 4, 256);
     L.off_if1 = o; o = align_up(o + ((size_t)ntx * nty + 1) * 4, 256);
+    L.off_clist = o; o = align_up(o + (size_t)ntiles * 4, 256);
+    L.off_flist = o; o = align_up(o + (size_t)ntiles * 4, 256);
     L.total = o;
     return RG_OK;
 }
@@ -279,7 +398,8 @@ extern "C" int rg_ctx_reserve(rg_ctx *c, int64_t nx, int64_t ny, int64_t nz, int
 template <class C>
 static int set_attrs()
 {
-    CK(cudaFuncSetAttribute(k_pass_a<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_a_full<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
     CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
     return RG_OK;
 }
@@ -300,9 +420,12 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.t4 = (uint32_t)(threshold & 0xFF) * 0x01010101u;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
     P.nseeds = nseeds;
+    memset(&c->last_tmap, 0, sizeof c->last_tmap);
+    P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, d_image - (size_t)zlo_ext * nx * ny, nx, ny, nz + zlo_ext + zhi_ext)) ? 1 : 0;
     P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
     P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
     P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
+    P.complex_list = (uint32_t *)(ws + L.off_clist); P.flag_list = (uint32_t *)(ws + L.off_flist);
     uint64_t *keys = (uint64_t *)(ws + L.off_keys), *keys2 = (uint64_t *)(ws + L.off_keys2);
     P.seed_keys = keys;
 
@@ -317,7 +440,8 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
         k_sort_small<<<1, 1024, 0, st>>>(keys, nseeds);
     }
     if (c->profile) cudaEventRecord(c->ev[1], st);
-    k_pass_a<C><<<L.ntiles, RG_THREADS, sizeof(TileSmem<C>), st>>>(P);
+    k_pass_a_fast<C><<<L.ntiles, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
+    k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
     int64_t items = (int64_t)L.ntiles * 3;
     int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
@@ -333,8 +457,13 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
 static int launch_finish(rg_ctx *c, cudaStream_t st)
 {
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
-    if (c->last_is2d) k_pass_c<Cfg2D><<<c->last_ntiles, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P);
-    else k_pass_c<Cfg3D><<<c->last_ntiles, RG_THREADS, sizeof(TileSmem<Cfg3D>), st>>>(c->last_P);
+    if (c->last_is2d) {
+        k_flag_tiles<Cfg2D><<<c->last_ntiles, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
+    } else {
+        k_flag_tiles<Cfg3D><<<c->last_ntiles, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
+    }
     if (c->profile) cudaEventRecord(c->ev[4], st);
     CK(cudaGetLastError());
     c->last_stream = st;
@@ -449,7 +578,7 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
     if (!c->last_counters) { if (stats) memset(stats, 0, 16); return RG_OK; }
     CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
     CK(cudaStreamSynchronize(c->last_stream));
-    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_FACE_MISMATCH]; stats[3] = 0; }
+    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX]; stats[3] = c->h_status[CTR_NFLAGGED]; }
     if (c->h_status[CTR_STATUS]) {
         snprintf(g_err, sizeof g_err, "engine self-check failed: status=0x%x mismatching faces=%u", c->h_status[CTR_STATUS], c->h_status[CTR_FACE_MISMATCH]);
         return RG_ERR_INTERNAL;

@@ -1,0 +1,309 @@
+/*
+ * rg_fast.h -- the cheap paths in front of the full tile passes of rg_core.h.
+ *
+ * Measured on B200 (profiles/r01_v1_ncu_summary.md) the full labelling pass is instruction bound:
+ * it builds three edge bit planes and runs a union-find over every run of every tile, although in
+ * the inputs the reference generates (rand()%20 noise around a few solids, raycast.cu:114-144)
+ * almost every component is a handful of voxels and only ~1 % of them reach a tile face.  So:
+ *
+ *   tile_pass_a_fast  one CTA per tile, ~56 KB smem (3 CTAs/SM): stage the tile, compute edge words
+ *                     ONLY on the six face layers, then let one thread per cross-tile edge (and per
+ *                     seed) walk its component directly on the staged bytes, at most WALK_MAX voxels.
+ *                     The walk returns the component's smallest voxel index -- the same
+ *                     representative the union-find of the full pass produces -- so nodes and face
+ *                     lists are emitted exactly as in rg_core.h.  A tile in which any walk overflows
+ *                     (a solid, a corridor ...) is appended to a work list and labelled by the full
+ *                     pass instead; nothing is written for it here.
+ *   flag_tiles        one small CTA per tile, no smem: decides whether any node of the tile ended up
+ *                     in the region (root == node 0); if not, streams zeros over the tile's mask, else
+ *                     appends the tile to the pass C work list.
+ *
+ * Same reference semantics as rg_core.h (region.c:493-533, raycast.cu:281-318); results are
+ * identical whichever path a tile takes.
+ */
+#pragma once
+#include "rg_core.h"
+
+namespace rg {
+
+enum { WALK_MAX = 16 };                       /* voxels a walk may visit before the tile is called complex */
+enum { FAST_ENT_MAX = 2048 };                 /* face-list entries the fast pass keeps per tile */
+
+template <class C>
+struct alignas(128) FastSmem {
+    uint8_t img[C::IMG_BYTES];
+    uint64_t mbar;
+    uint32_t fmask[C::FW_TOTAL];
+    uint16_t fprefix[C::FW_TOTAL + 2];
+    uint16_t ent_root[FAST_ENT_MAX];
+    uint32_t openbits[C::NW], seedbits[C::NW];
+    uint16_t wprefix[C::NW];
+    uint32_t scal[16];
+    uint32_t scan_scratch[40];
+    static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit");
+};
+
+/* ---- a tiny queue of 16-bit entries packed in four 64-bit registers ---- */
+struct WalkQ { uint64_t a, b, c, d; };
+RG_FN void wq_clear(WalkQ &w) { w.a = w.b = w.c = w.d = 0; }
+RG_FN void wq_set(WalkQ &w, int i, uint32_t v)
+{
+    const uint64_t e = (uint64_t)(v | 0x8000u) << (16 * (i & 3));
+    const int k = i >> 2;
+    w.a |= (k == 0) ? e : 0; w.b |= (k == 1) ? e : 0; w.c |= (k == 2) ? e : 0; w.d |= (k == 3) ? e : 0;
+}
+RG_FN uint32_t wq_get(const WalkQ &w, int i)
+{
+    const int k = i >> 2;
+    const uint64_t x = (k == 0) ? w.a : (k == 1) ? w.b : (k == 2) ? w.c : w.d;
+    return (uint32_t)(x >> (16 * (i & 3))) & 0x7FFFu;
+}
+RG_FN bool wq_zero16(uint64_t x) { return ((x - 0x0001000100010001ULL) & ~x & 0x8000800080008000ULL) != 0; }
+RG_FN bool wq_has(const WalkQ &w, uint32_t v)
+{
+    const uint64_t pat = (uint64_t)(v | 0x8000u) * 0x0001000100010001ULL;   /* a zero half-word of q ^ pat <=> v is queued */
+    return wq_zero16(w.a ^ pat) || wq_zero16(w.b ^ pat) || wq_zero16(w.c ^ pat) || wq_zero16(w.d ^ pat);
+}
+
+/* Walk the component of voxel `start` on the staged bytes (6- or 4-connectivity inside the tile's
+ * valid extent).  Returns false if it has more than WALK_MAX voxels; else root = smallest voxel
+ * index, n = size, and the visited voxels are left in wq. */
+template <class C>
+RG_FN bool walk_component(const uint8_t *img, int vx, int vy, int vz, int tmode, uint32_t t4, uint32_t start,
+                          WalkQ &wq, int &n, uint32_t &root)
+{
+    n = 1; root = start;
+    const int ndir = C::HZ ? 6 : 4;
+    {   /* most components are a single voxel: look at the start voxel's neighbours before paying for a queue */
+        const int x = (int)(start % C::TX), y = (int)((start / C::TX) % C::TY), z = (int)(start / (C::TX * C::TY));
+        const uint8_t *p = img + img_off<C>(x, y, z);
+        const uint32_t a = *p;
+        bool any = (x > 0 && similar1(a, p[-1], tmode, t4)) | (x + 1 < vx && similar1(a, p[1], tmode, t4))
+                 | (y > 0 && similar1(a, p[-C::RS], tmode, t4)) | (y + 1 < vy && similar1(a, p[C::RS], tmode, t4));
+        if (C::HZ) any = any | (z > 0 && similar1(a, p[-C::PS], tmode, t4)) | (z + 1 < vz && similar1(a, p[C::PS], tmode, t4));
+        if (!any) return true;
+    }
+    wq_clear(wq);
+    wq_set(wq, 0, start);
+    int head = 0;
+    while (head < n) {
+        const uint32_t v = wq_get(wq, head++);
+        const int x = (int)(v % C::TX), y = (int)((v / C::TX) % C::TY), z = (int)(v / (C::TX * C::TY));
+        const uint8_t *p = img + img_off<C>(x, y, z);
+        const uint32_t a = *p;
+        for (int d = 0; d < ndir; d++) {
+            int off; uint32_t u; bool ok;
+            if (d == 0) { ok = x > 0; off = -1; u = v - 1; }
+            else if (d == 1) { ok = x + 1 < vx; off = 1; u = v + 1; }
+            else if (d == 2) { ok = y > 0; off = -C::RS; u = v - C::TX; }
+            else if (d == 3) { ok = y + 1 < vy; off = C::RS; u = v + C::TX; }
+            else if (d == 4) { ok = z > 0; off = -C::PS; u = v - C::TX * C::TY; }
+            else { ok = z + 1 < vz; off = C::PS; u = v + C::TX * C::TY; }
+            if (!ok || !similar1(a, p[off], tmode, t4)) continue;
+            if (wq_has(wq, u)) continue;
+            if (n == WALK_MAX) return false;
+            wq_set(wq, n++, u);
+            if (u < root) root = u;
+        }
+    }
+    return true;
+}
+
+/* voxel (tile-local linear index) on this side of cross-tile edge `b` of face word (f, idx) */
+template <class C>
+RG_FN uint32_t face_voxel(int f, int idx, int b, int vz)
+{
+    int x, y, z;
+    if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
+    else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? C::TY - 1 : 0; }
+    else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
+    return (uint32_t)((z * C::TY + y) * C::TX + x);
+}
+
+/* cross-tile edge masks of the six faces, from the staged bytes (the same words build_edges<FACES>
+ * produces, without touching the interior) */
+template <class C, class Exec>
+RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint32_t *fmask, int64_t x0, int64_t y0, int64_t z0)
+{
+    const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
+    const int tmode = P.tmode; const uint32_t t4 = P.t4;
+    const int vy = (int)((ny - y0) < C::TY ? (ny - y0) : C::TY);
+    const int vz = (int)((nz - z0) < C::TZ ? (nz - z0) : C::TZ);
+    const bool has_yp = y0 + C::TY < ny, has_ym = y0 > 0;
+    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && P.zhi_ext));
+    const bool has_zm = C::HZ && (z0 > 0 || P.zlo_ext);
+    const bool has_xp = x0 + C::TX < nx, has_xm = x0 > 0;
+    /* y faces: item = (side, z, wx); z faces: item = (side, y, wx) */
+    ex.pfor(2 * C::FYW + 2 * C::FZW, [&](int it) {
+        const bool zface = it >= 2 * C::FYW;
+        int r = zface ? it - 2 * C::FYW : it;
+        const int nper = zface ? C::FZW : C::FYW;
+        const int side = r / nper; r %= nper;
+        const int wx = r % C::WX, o = r / C::WX;                   /* o = z for y faces, y for z faces */
+        int y, z, step, f;
+        if (!zface) {
+            if (side ? !has_yp : !has_ym) return;
+            z = o; y = side ? C::TY - 1 : 0; step = side ? C::RS : -C::RS; f = side ? F_YP : F_YM;
+            if (z >= vz) return;
+        } else {
+            if (side ? !has_zp : !has_zm) return;
+            y = o; z = side ? vz - 1 : 0; step = side ? C::PS : -C::PS; f = side ? F_ZP : F_ZM;
+            if (y >= vy) return;
+        }
+        const uint32_t vmask = valid_bits(nx - (x0 + 32 * wx));
+        if (!vmask) return;
+        const uint8_t *rowp = img + img_off<C>(32 * wx, y, z);
+        uint32_t a[8], b[8];
+        load8(rowp, a); load8(rowp + step, b);
+        const uint32_t m = edge_word(a, b, tmode, t4) & vmask;
+        if (m) fmask[C::fw_off(f) + o * C::WX + wx] = dedupe(m, xedges_within(a, tmode, t4), xedges_within(b, tmode, t4));
+    });
+    /* x faces: one bit per (y, z) */
+    ex.pfor(2 * C::TY * C::TZ, [&](int it) {
+        const int side = it / (C::TY * C::TZ), q = it % (C::TY * C::TZ);
+        const int y = q % C::TY, z = q / C::TY;
+        if ((side ? !has_xp : !has_xm) || y >= vy || z >= vz) return;
+        const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
+        const uint32_t own = o[0], other = o[side ? 1 : -1];
+        if (similar1(own, other, tmode, t4)) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
+    });
+}
+
+/* this tile's slice [lo, hi) of the sorted seed keys */
+RG_FN void seed_range(const Params &P, uint32_t tile, uint32_t &lo_out, uint32_t &hi_out)
+{
+    uint64_t lo_key = (uint64_t)tile << 16, hi_key = ((uint64_t)tile + 1) << 16;
+    int lo = 0, hi = P.nseeds;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < lo_key) lo = mid + 1; else hi = mid; }
+    int a = lo; hi = P.nseeds;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
+    lo_out = (uint32_t)a; hi_out = (uint32_t)lo;
+}
+
+/* ================================================================ fast labelling pass */
+template <class C, class Exec>
+RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C> &s)
+{
+    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
+    const int vx = (int)((P.nx - x0) < C::TX ? (P.nx - x0) : C::TX);
+    const int vy = (int)((P.ny - y0) < C::TY ? (P.ny - y0) : C::TY);
+    const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
+
+    if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
+    ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
+    ex.pfor(C::NW, [&](int i) { s.openbits[i] = 0; s.seedbits[i] = 0; });
+    if (ex.tid() == 0) {
+        uint32_t lo, hi; seed_range(P, tile, lo, hi);
+        s.scal[SC_SEED_LO] = lo; s.scal[SC_SEED_HI] = hi; s.scal[SC_OVERFLOW] = 0; s.scal[SC_COMPLEX] = 0; s.scal[SC_UNIFORM] = 0;
+    }
+    ex.tile_wait(&s.mbar);
+    ex.sync();
+    /* a tile whose own voxels are all equal is one component with representative 0 (solid interiors) */
+    bool uniform = false;
+    if (P.fast16 && P.tmode >= 1) {
+        const uint32_t pat = (uint32_t)s.img[img_off<C>(0, 0, 0)] * 0x01010101u;
+        bool differs = false;
+        ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+            int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+            if (y >= vy || z >= vz || 16 * c >= vx) return;
+            u32x4 q = ld128(&s.img[img_off<C>(16 * c, y, z)]);
+            if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) differs = true;
+        });
+        uniform = !ex.sync_or(differs);
+    }
+    build_face_masks<C>(ex, P, s.img, s.fmask, x0, y0, z0);
+    ex.sync();
+    uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
+    if (ex.tid() == 0) { s.fprefix[C::FW_TOTAL] = (uint16_t)etot; s.scal[SC_ETOT] = etot; }
+    ex.sync();
+    if (etot > FAST_ENT_MAX) {                                      /* uniform: every thread sees the same total */
+        if (ex.tid() == 0) P.complex_list[atomic_add(&P.counters[CTR_NCOMPLEX], 1u)] = tile;
+        return;
+    }
+    if (uniform) {
+        const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
+        ex.pfor((int)etot, [&](int e) { s.ent_root[e] = 0; });
+        if (ex.tid() == 0) {
+            if (etot || seeded) s.openbits[0] = 1u;
+            if (seeded) s.seedbits[0] = 1u;
+            s.scal[SC_UNIFORM] = 1;
+        }
+        ex.sync();
+        emit_nodes<C>(ex, P, tile, s);
+        return;
+    }
+    /* start voxel of every cross-tile edge, in list order ... */
+    ex.pfor(C::FW_TOTAL, [&](int fw) {
+        uint32_t m = s.fmask[fw];
+        if (!m) return;
+        int f = 0; while (fw >= C::fw_off(f + 1)) f++;
+        const int idx = fw - C::fw_off(f);
+        uint32_t slot = s.fprefix[fw];
+        while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vz); }
+    });
+    ex.sync();
+    /* ... then one walk per edge, one thread each */
+    ex.pfor((int)etot, [&](int e) {
+        WalkQ wq; int n; uint32_t root;
+        if (!walk_component<C>(s.img, vx, vy, vz, P.tmode, P.t4, s.ent_root[e], wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+        atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
+        s.ent_root[e] = (uint16_t)root;
+    });
+    /* ... and per seed */
+    {
+        const int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
+        ex.pfor(hi - lo, [&](int i) {
+            WalkQ wq; int n; uint32_t root;
+            if (!walk_component<C>(s.img, vx, vy, vz, P.tmode, P.t4, (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
+            atomic_or(&s.seedbits[root >> 5], 1u << (root & 31));
+        });
+    }
+    ex.sync();
+    if (s.scal[SC_COMPLEX]) {
+        if (ex.tid() == 0) P.complex_list[atomic_add(&P.counters[CTR_NCOMPLEX], 1u)] = tile;
+        return;
+    }
+    emit_nodes<C>(ex, P, tile, s);
+}
+
+/* the full pass over the tiles the fast pass gave up on (persistent CTAs) */
+template <class C, class Exec>
+RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
+{
+    const uint32_t n = P.counters[CTR_NCOMPLEX];
+    for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
+        tile_pass_a<C>(ex, P, P.complex_list[i], s);
+        ex.sync();
+    }
+}
+
+/* ================================================================ region tiles vs. empty tiles */
+template <class C, class Exec>
+RG_FN void flag_tile(Exec &ex, const Params &P, uint32_t tile)
+{
+    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
+    const TileRec rc = P.rec[tile];
+    bool mine = false;
+    ex.pfor((int)rc.nnodes, [&](int i) { if (find32(P.nparent, rc.node_base + (uint32_t)i) == 0u) mine = true; });
+    if (ex.sync_or(mine)) {
+        if (rc.uniform) { fill_tile<C>(ex, P, x0, y0, z0, 1u); return; }      /* whole tile is one region component */
+        if (ex.tid() == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
+        return;
+    }
+    zero_tile<C>(ex, P, x0, y0, z0);
+}
+
+template <class C, class Exec>
+RG_FN void pass_c_list(Exec &ex, const Params &P, TileSmem<C> &s)
+{
+    const uint32_t n = P.counters[CTR_NFLAGGED];
+    for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
+        tile_pass_c<C>(ex, P, P.flag_list[i], s);
+        ex.sync();
+    }
+}
+
+} // namespace rg

@@ -63,7 +63,23 @@ RG_FN void st128_stream(void *p, u32x4 v)
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+/* asynchronous global->shared copies (LDGSTS): many chunks in flight per thread, no register staging.
+   `ok` == false zero-fills the destination (src-size 0) */
+RG_FN void cp_async16(void *smem_dst, const void *gsrc, bool ok)
+{
+    uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(gsrc), "r"(ok ? 16 : 0) : "memory");
+}
+RG_FN void cp_async4(void *smem_dst, const void *gsrc, bool ok)
+{
+    uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" :: "r"(d), "l"(gsrc), "r"(ok ? 4 : 0) : "memory");
+}
+RG_FN void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 #else
+RG_FN void cp_async16(void *smem_dst, const void *gsrc, bool ok) { if (ok) memcpy(smem_dst, gsrc, 16); else memset(smem_dst, 0, 16); }
+RG_FN void cp_async4(void *smem_dst, const void *gsrc, bool ok) { if (ok) memcpy(smem_dst, gsrc, 4); else memset(smem_dst, 0, 4); }
+RG_FN void cp_async_wait_all() {}
 RG_FN int popc(uint32_t x) { return __builtin_popcount(x); }
 RG_FN int clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
 RG_FN int ffs1(uint32_t x) { return __builtin_ffs((int)x); }

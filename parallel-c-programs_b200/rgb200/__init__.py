@@ -227,7 +227,7 @@ class Context:
         st = (ctypes.c_uint32 * 4)()
         rc = self.lib.rg_ctx_status(self.handle, st)
         _check(self.lib, rc, "rg_ctx_status")
-        return {"nodes": st[0], "status": st[1], "face_mismatch": st[2]}
+        return {"nodes": st[0], "status": st[1], "complex_tiles": st[2], "region_tiles": st[3]}
 
     def profile(self, enable=True):
         _check(self.lib, self.lib.rg_ctx_profile(self.handle, 1 if enable else 0), "rg_ctx_profile")

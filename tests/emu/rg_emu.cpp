@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <vector>
 #include "../../parallel-c-programs_b200/csrc/rg_core.h"
+#include "../../parallel-c-programs_b200/csrc/rg_fast.h"
 #include "../../parallel-c-programs_b200/csrc/rg_slab_core.h"
 
 using namespace rg;
@@ -23,6 +24,11 @@ struct HostExec {
     template <class F> void pfor(int n, F f) { for (int i = 0; i < n; i++) f(i); }
     template <class F> void gpfor(int64_t n, F f) { for (int64_t i = 0; i < n; i++) f(i); }
     void sync() {}
+    bool sync_or(bool p) { return p; }
+    template <class C> bool tma_tile(const Params &, uint8_t *, uint64_t *, int64_t, int64_t, int64_t) { return false; }
+    void tile_wait(uint64_t *) {}
+    uint32_t bid() const { return 0; }
+    uint32_t nblk() const { return 1; }
     template <class F> uint32_t scan16(int n, F count, uint16_t *out, uint32_t *)
     {
         uint32_t run = 0;
@@ -37,9 +43,12 @@ struct HostExec {
     }
 };
 
+static int g_force_full = 0;      /* 1: label every tile with the full pass (fast pass off) */
+extern "C" void emu_force_full(int v) { g_force_full = v; }
+
 struct EmuState {
     std::vector<TileRec> rec; std::vector<uint16_t> ent; std::vector<uint32_t> npar; std::vector<uint16_t> nrep;
-    std::vector<uint64_t> keys; uint32_t counters[CTR_WORDS];
+    std::vector<uint64_t> keys; std::vector<uint32_t> clist, flist; uint32_t counters[CTR_WORDS];
     Params P;
 };
 
@@ -57,6 +66,8 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     size_t cap = 1 + ntiles * C::ENT_MAX + (size_t)nseeds;
     E.rec.assign(ntiles, TileRec()); E.ent.assign(ntiles * C::ENT_MAX, 0); E.npar.assign(cap, 0xDEADBEEF); E.nrep.assign(cap, 0);
     E.keys.assign((size_t)std::max(nseeds, 1), ~0ull);
+    E.clist.assign(ntiles, 0); E.flist.assign(ntiles, 0);
+    P.complex_list = E.clist.data(); P.flag_list = E.flist.data();
     P.rec = E.rec.data(); P.ent = E.ent.data(); P.nparent = E.npar.data(); P.nrep = E.nrep.data();
     P.counters = E.counters; P.node_cap = (uint32_t)cap; P.nseeds = nseeds; P.seed_keys = E.keys.data();
     HostExec ex;
@@ -69,17 +80,23 @@ template <class C> static void emu_label(EmuState &E)
 {
     HostExec ex; const Params &P = E.P;
     uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
-    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(16, (sizeof(TileSmem<C>) + 15) / 16 * 16);
-    for (uint32_t t = 0; t < ntiles; t++) { memset(s, 0xA5, sizeof *s); tile_pass_a<C>(ex, P, t, *s); }
+    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(128, (sizeof(TileSmem<C>) + 127) / 128 * 128);
+    FastSmem<C> *f = (FastSmem<C> *)aligned_alloc(128, (sizeof(FastSmem<C>) + 127) / 128 * 128);
+    if (g_force_full) { for (uint32_t t = 0; t < ntiles; t++) E.clist[t] = t; E.counters[CTR_NCOMPLEX] = ntiles; }
+    else for (uint32_t t = 0; t < ntiles; t++) { memset(f, 0xA5, sizeof *f); tile_pass_a_fast<C>(ex, P, t, *f); }
+    memset(s, 0xA5, sizeof *s);
+    pass_a_full_list<C>(ex, P, *s);
     merge_faces<C>(ex, P);
-    free(s);
+    free(s); free(f);
 }
 template <class C> static void emu_finish(EmuState &E)
 {
     HostExec ex; const Params &P = E.P;
     uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
-    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(16, (sizeof(TileSmem<C>) + 15) / 16 * 16);
-    for (uint32_t t = 0; t < ntiles; t++) { memset(s, 0x5A, sizeof *s); tile_pass_c<C>(ex, P, t, *s); }
+    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(128, (sizeof(TileSmem<C>) + 127) / 128 * 128);
+    for (uint32_t t = 0; t < ntiles; t++) flag_tile<C>(ex, P, t);
+    memset(s, 0x5A, sizeof *s);
+    pass_c_list<C>(ex, P, *s);
     free(s);
 }
 
@@ -91,7 +108,7 @@ static int emu_grow_t(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, 
     emu_setup<C>(E, image, nx, ny, nz, 0, 0, seeds, nseeds, T, mask);
     emu_label<C>(E);
     emu_finish<C>(E);
-    if (stats) { stats[0] = E.counters[CTR_NODES]; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_FACE_MISMATCH]; stats[3] = (uint32_t)E.rec.size(); }
+    if (stats) { stats[0] = E.counters[CTR_NODES]; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX]; stats[3] = (uint32_t)E.rec.size(); }
     return E.counters[CTR_STATUS] ? -4 : 0;
 }
 

@@ -120,3 +120,54 @@ def test_emu_slabs_serpentine(emu, oracle, G):
     img, seeds, T = oracle.synth("c3", 20)
     got, _ = run_emu(emu, 2, img, seeds, T, slabs=G)
     assert (got == oracle.grow(img, seeds, T)).all()
+
+
+def test_emu_fast_and_full_paths_mix(emu, oracle):
+    """sparse noise tiles take the fast (walker) pass, solid tiles the full pass; neighbours on different
+    paths must still agree on their shared face lists"""
+    img, seeds, T = oracle.synth("c4", 96, 0x5EED0004)
+    want = oracle.grow(img, seeds, T)
+    got, st = run_emu(emu, 1, img, seeds, T)
+    assert (got == want).all()
+    ncomplex, ntiles = int(st[2]), int(st[3])
+    assert 0 < ncomplex < ntiles, (ncomplex, ntiles)
+    emu.emu_force_full(1)
+    try:
+        got2, st2 = run_emu(emu, 1, img, seeds, T)
+    finally:
+        emu.emu_force_full(0)
+    assert int(st2[2]) == ntiles and (got2 == want).all()
+    assert int(st2[0]) == int(st[0])                      # same number of coarse nodes whichever path labelled the tiles
+
+
+@pytest.mark.parametrize("levels", [2, 4, 12, 40])
+def test_emu_walk_limit_boundary(emu, oracle, levels):
+    """component sizes around WALK_MAX: some walks overflow, some do not"""
+    rng = np.random.default_rng(levels)
+    img = rng.integers(0, levels, size=(12, 20, 96), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 96, 10), rng.integers(0, 20, 10), rng.integers(0, 12, 10)], 1)
+    got, st = run_emu(emu, 1, img, seeds, 1)
+    assert (got == oracle.grow(img, seeds, 1)).all()
+    got, st = run_emu(emu, 0, img, seeds, 1)
+    assert (got == oracle.grow(img, seeds, 1)).all()
+
+
+@pytest.mark.parametrize("cfg", [0, 1, 2])
+def test_emu_uniform_tiles(emu, oracle, cfg):
+    """tiles lying wholly inside a solid take the uniform shortcut (one component, representative 0,
+    pass C fills ones without reading the image); their neighbours are mixed / noise tiles"""
+    rng = np.random.default_rng(9 + cfg)
+    img = rng.integers(0, 20, size=(48, 96, 192), dtype=np.uint8)
+    img[4:44, 10:90, 20:180] = 77                       # a solid spanning many whole tiles
+    img[10:12, 30:40, 64:128] = 3                       # a hole touching whole-tile boundaries
+    seeds = [[100, 50, 20], [0, 0, 0], [191, 95, 47]]
+    want = oracle.grow(img, seeds, 1)
+    got, st = run_emu(emu, cfg, img, seeds, 1)
+    assert (got == want).all()
+    assert want[20, 50, 100] == 1 and want.sum() > 40 * 80 * 160 - 2 * 10 * 64 - 10
+    # same image, seed only in the noise: the solid stays out although its tiles are uniform
+    got2, _ = run_emu(emu, cfg, img, [[0, 0, 0]], 1)
+    assert (got2 == oracle.grow(img, [[0, 0, 0]], 1)).all() and got2[20, 50, 100] == 0
+    # threshold 0: no edges at all, the shortcut must not fire
+    got3, _ = run_emu(emu, cfg, img, seeds, 0)
+    assert got3.sum() == 3
