@@ -57,6 +57,7 @@ struct TileCfg {
     static constexpr int ENT_MAX = 2 * (FXN + FYN + FZN);   /* face-list entries per tile, worst case */
     static_assert(TX % 32 == 0, "rows are whole words");
     static_assert(NV <= 65536, "16-bit tile-local indices");
+    static_assert(NW % 4 == 0, "bit sets are cleared 16 bytes at a time");
     RG_MFN static constexpr int fw_off(int f)
     {
         return f == 0 ? 0 : f == 1 ? FXW : f == 2 ? 2 * FXW : f == 3 ? 2 * FXW + FYW
@@ -85,6 +86,7 @@ struct Params {
     int32_t zlo_ext, zhi_ext;    /* slab has a neighbour slab below / above (multi-GPU) */
     int32_t tmode;               /* 0: T <= 0 (no edges)  1: 1..255  2: T >= 256 (all edges) */
     uint32_t t4;                 /* T replicated into 4 bytes */
+    uint32_t thr;                /* scalar form: similar <=> |a-b| < thr  (0, T or 256) */
     int32_t fast16;              /* nx % 16 == 0 and both buffers 16-byte aligned */
     int32_t use_tma;             /* tiles are staged by one cp.async.bulk.tensor (needs fast16) */
     const uint64_t *seed_keys;   /* sorted (tile << 16 | voxel-in-tile); ~0 = dropped */
@@ -118,7 +120,7 @@ struct alignas(128) TileSmem {
     uint32_t scal[16];
     uint32_t scan_scratch[40];
 };
-enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8 };
+enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8, SC_NSLOW = 9 };
 
 /* ---------------------------------------------------------------- small helpers */
 RG_FN uint32_t valid_bits(int64_t n) { return n >= 32 ? 0xFFFFFFFFu : n <= 0 ? 0u : ((1u << n) - 1u); }

@@ -23,7 +23,9 @@ using namespace rg;
 /* ------------------------------------------------------------------ Exec for a CUDA block */
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+template <int NT>
 struct DevExec {
+    bool grid3d = false;                    /* tile coordinates come straight from blockIdx */
     const CUtensorMap *tmap = nullptr;      /* image descriptor (kernel parameter) */
     uint32_t phase = 0;                     /* parity of the next mbarrier completion */
     bool tma_pending = false;
@@ -75,41 +77,47 @@ struct DevExec {
     __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
     template <class F> __device__ __forceinline__ void pfor(int n, F f)
     {
-        for (int i = (int)threadIdx.x; i < n; i += (int)blockDim.x) f(i);
+        for (int i = (int)threadIdx.x; i < n; i += NT) f(i);
     }
     template <class F> __device__ __forceinline__ void gpfor(int64_t n, F f)
     {
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) f(i);
+        for (int64_t i = (int64_t)blockIdx.x * NT + threadIdx.x; i < n; i += (int64_t)gridDim.x * NT) f(i);
     }
     __device__ __forceinline__ void sync() { __syncthreads(); }
     __device__ __forceinline__ bool sync_or(bool p) { return __syncthreads_or(p ? 1 : 0) != 0; }
+    template <class C> __device__ __forceinline__ void origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz) const
+    {
+        if (grid3d) { tx = (int)blockIdx.x; ty = (int)blockIdx.y; tz = (int)blockIdx.z; } else tile_origin<C>(P, tile, tx, ty, tz);
+    }
     __device__ __forceinline__ uint32_t bid() const { return blockIdx.x; }
     __device__ __forceinline__ uint32_t nblk() const { return gridDim.x; }
-    /* block-wide exclusive scan of count(i), i < n, into out[i]; returns the total to every thread */
+    /* block-wide exclusive scan of count(i), i < n, into out[i]; returns the total to every thread.
+       Each thread owns a contiguous run of ceil(n / blockDim) items, so one shuffle scan covers the block. */
     template <class T, class F> __device__ __forceinline__ uint32_t scan(int n, F count, T *out, uint32_t *scratch)
     {
-        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-        uint32_t base = 0;
-        for (int start = 0; start < n; start += (int)blockDim.x) {
-            int i = start + (int)threadIdx.x;
-            uint32_t c = i < n ? count(i) : 0u, incl = c;
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarp = NT >> 5;
+        const int per = (n + NT - 1) / NT;
+        const int i0 = (int)threadIdx.x * per;
+        uint32_t local = 0;
+        for (int k = 0; k < per; k++) if (i0 + k < n) local += count(i0 + k);
+        uint32_t incl = local;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
-            if (lane == 31) scratch[wid] = incl;
-            __syncthreads();
-            if (wid == 0) {
-                uint32_t v = lane < nwarp ? scratch[lane] : 0u, inc2 = v;
+        for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d); if (lane >= d) incl += t; }
+        if (lane == 31) scratch[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t v = lane < nwarp ? scratch[lane] : 0u, inc2 = v;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc2, d); if (lane >= d) inc2 += t; }
-                scratch[lane] = inc2 - v;
-                if (lane == 31) scratch[32] = inc2;
-            }
-            __syncthreads();
-            if (i < n) out[i] = (T)(base + scratch[wid] + incl - c);
-            base += scratch[32];
-            __syncthreads();
+            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc2, d); if (lane >= d) inc2 += t; }
+            scratch[lane] = inc2 - v;
+            if (lane == 31) scratch[32] = inc2;
         }
-        return base;
+        __syncthreads();
+        uint32_t run = scratch[wid] + incl - local;
+        for (int k = 0; k < per; k++) if (i0 + k < n) { out[i0 + k] = (T)run; run += count(i0 + k); }
+        const uint32_t total = scratch[32];
+        __syncthreads();
+        return total;
     }
     template <class F> __device__ __forceinline__ uint32_t scan16(int n, F count, uint16_t *out, uint32_t *scratch) { return scan<uint16_t>(n, count, out, scratch); }
     template <class F> __device__ __forceinline__ uint32_t scan32(int n, F count, uint32_t *out, uint32_t *scratch) { return scan<uint32_t>(n, count, out, scratch); }
@@ -127,9 +135,11 @@ __global__ void __launch_bounds__(RG_FAST_THREADS, 3) k_pass_a_fast(const Params
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     FastSmem<C> &s = *reinterpret_cast<FastSmem<C> *>(smem_raw);
-    DevExec ex; ex.tmap = &tmap;
+    DevExec<RG_FAST_THREADS> ex; ex.tmap = &tmap;
+    ex.grid3d = gridDim.y * gridDim.z > 1 || (P.nty == 1 && P.ntz == 1);
     if (P.use_tma) ex.mbar_init(&s.mbar);
-    tile_pass_a_fast<C>(ex, P, blockIdx.x, s);
+    const uint32_t tile = ex.grid3d ? (blockIdx.z * (uint32_t)P.nty + blockIdx.y) * (uint32_t)P.ntx + blockIdx.x : blockIdx.x;
+    tile_pass_a_fast<C>(ex, P, tile, s);
 }
 
 /* pass A, full path: the tiles the fast path listed (persistent CTAs) */
@@ -138,7 +148,7 @@ __global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a_full(const Params P, c
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
-    DevExec ex; ex.tmap = &tmap;
+    DevExec<RG_THREADS> ex; ex.tmap = &tmap;
     if (P.use_tma) ex.mbar_init(&s.mbar);
     pass_a_full_list<C>(ex, P, s);
 }
@@ -147,8 +157,10 @@ __global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a_full(const Params P, c
 template <class C>
 __global__ void __launch_bounds__(RG_FLAG_THREADS) k_flag_tiles(const Params P)
 {
-    DevExec ex;
-    flag_tile<C>(ex, P, blockIdx.x);
+    DevExec<RG_FLAG_THREADS> ex;
+    ex.grid3d = gridDim.y * gridDim.z > 1 || (P.nty == 1 && P.ntz == 1);
+    const uint32_t tile = ex.grid3d ? (blockIdx.z * (uint32_t)P.nty + blockIdx.y) * (uint32_t)P.ntx + blockIdx.x : blockIdx.x;
+    flag_tile<C>(ex, P, tile);
 }
 
 /* pass C, part 2: the listed tiles (persistent CTAs) */
@@ -157,7 +169,7 @@ __global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P, const 
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
-    DevExec ex; ex.tmap = &tmap;
+    DevExec<RG_THREADS> ex; ex.tmap = &tmap;
     if (P.use_tma) ex.mbar_init(&s.mbar);
     pass_c_list<C>(ex, P, s);
 }
@@ -165,14 +177,14 @@ __global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P, const 
 template <class C>
 __global__ void __launch_bounds__(256) k_merge(const Params P)
 {
-    DevExec ex;
+    DevExec<256> ex;
     merge_faces<C>(ex, P);
 }
 
 template <class C>
 __global__ void __launch_bounds__(256) k_seed_keys(const Params P, const int32_t *seeds_xyz, uint64_t *keys)
 {
-    DevExec ex;
+    DevExec<256> ex;
     if (blockIdx.x == 0 && threadIdx.x == 0) reset_counters(P);
     make_seed_keys<C>(ex, P, seeds_xyz, keys);
 }
@@ -210,30 +222,30 @@ template <class C>
 __global__ void __launch_bounds__(1024) k_export_offsets(const Params P, int side, uint32_t *tile_off, uint32_t *count_out)
 {
     __shared__ uint32_t scratch[40];
-    DevExec ex;
+    DevExec<1024> ex;
     export_offsets<C>(ex, P, side, tile_off, count_out, scratch);
 }
 template <class C>
 __global__ void __launch_bounds__(128) k_export_entries(const Params P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t *counts3)
 {
-    DevExec ex;
+    DevExec<128> ex;
     if (blockIdx.x == 0 && threadIdx.x == 0) counts3[2] = P.counters[CTR_NODES];
     export_entries<C>(ex, P, side, tile_off, out_roots);
 }
 __global__ void __launch_bounds__(256) k_resolve_init(uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
 {
-    DevExec ex;
+    DevExec<256> ex;
     if (blockIdx.x == 0 && threadIdx.x == 0) xpar[0] = 0;
     resolve_init(ex, xpar, roots, n, off);
 }
 __global__ void __launch_bounds__(256) k_resolve_union(uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint32_t *b, uint32_t offb, uint32_t n)
 {
-    DevExec ex;
+    DevExec<256> ex;
     resolve_union(ex, xpar, a, offa, b, offb, n);
 }
 __global__ void __launch_bounds__(256) k_resolve_apply(const Params P, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
 {
-    DevExec ex;
+    DevExec<256> ex;
     resolve_apply(ex, P, xpar, roots, n, off);
 }
 
@@ -261,6 +273,7 @@ struct rg_ctx {
     bool attr_set;
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
+    dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     bool profile; cudaEvent_t ev[5]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
 };
@@ -418,6 +431,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.zlo_ext = zlo_ext; P.zhi_ext = zhi_ext;
     P.tmode = threshold <= 0 ? 0 : threshold >= 256 ? 2 : 1;
     P.t4 = (uint32_t)(threshold & 0xFF) * 0x01010101u;
+    P.thr = threshold <= 0 ? 0u : threshold >= 256 ? 256u : (uint32_t)threshold;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
     P.nseeds = nseeds;
     memset(&c->last_tmap, 0, sizeof c->last_tmap);
@@ -440,7 +454,10 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
         k_sort_small<<<1, 1024, 0, st>>>(keys, nseeds);
     }
     if (c->profile) cudaEventRecord(c->ev[1], st);
-    k_pass_a_fast<C><<<L.ntiles, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
+    const bool g3 = L.nty <= 65535 && L.ntz <= 65535;
+    const dim3 tile_grid = g3 ? dim3((unsigned)L.ntx, (unsigned)L.nty, (unsigned)L.ntz) : dim3(L.ntiles, 1, 1);
+    c->last_grid = tile_grid;
+    k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
     k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
     int64_t items = (int64_t)L.ntiles * 3;
@@ -458,10 +475,10 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
 {
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
     if (c->last_is2d) {
-        k_flag_tiles<Cfg2D><<<c->last_ntiles, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
         k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
     } else {
-        k_flag_tiles<Cfg3D><<<c->last_ntiles, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_flag_tiles<Cfg3D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
         k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
     }
     if (c->profile) cudaEventRecord(c->ev[4], st);

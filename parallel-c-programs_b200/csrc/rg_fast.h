@@ -36,7 +36,8 @@ struct alignas(128) FastSmem {
     uint32_t fmask[C::FW_TOTAL];
     uint16_t fprefix[C::FW_TOTAL + 2];
     uint16_t ent_root[FAST_ENT_MAX];
-    uint32_t openbits[C::NW], seedbits[C::NW];
+    alignas(16) uint32_t openbits[C::NW];
+    alignas(16) uint32_t seedbits[C::NW];
     uint16_t wprefix[C::NW];
     uint32_t scal[16];
     uint32_t scan_scratch[40];
@@ -59,52 +60,55 @@ RG_FN uint32_t wq_get(const WalkQ &w, int i)
     return (uint32_t)(x >> (16 * (i & 3))) & 0x7FFFu;
 }
 RG_FN bool wq_zero16(uint64_t x) { return ((x - 0x0001000100010001ULL) & ~x & 0x8000800080008000ULL) != 0; }
-RG_FN bool wq_has(const WalkQ &w, uint32_t v)
+RG_FN bool wq_has(const WalkQ &w, uint32_t v, int n)
 {
     const uint64_t pat = (uint64_t)(v | 0x8000u) * 0x0001000100010001ULL;   /* a zero half-word of q ^ pat <=> v is queued */
-    return wq_zero16(w.a ^ pat) || wq_zero16(w.b ^ pat) || wq_zero16(w.c ^ pat) || wq_zero16(w.d ^ pat);
+    bool hit = wq_zero16(w.a ^ pat);
+    if (n > 4) {                                                            /* rarely: most components have <= 4 voxels */
+        hit = hit || wq_zero16(w.b ^ pat);
+        if (n > 8) hit = hit || wq_zero16(w.c ^ pat) || wq_zero16(w.d ^ pat);
+    }
+    return hit;
+}
+
+/* which in-tile neighbours of voxel v are similar to it: one bit per direction (-x +x -y +y -z +z) */
+template <class C>
+RG_FN uint32_t neighbour_mask(const uint8_t *img, int vx, int vy, int vz, uint32_t thr, uint32_t v)
+{
+    const int x = (int)(v % C::TX), y = (int)((v / C::TX) % C::TY), z = (int)(v / (C::TX * C::TY));
+    const uint8_t *p = img + img_off<C>(x, y, z);
+    const uint32_t a = *p;
+    uint32_t nb = (uint32_t)(x > 0 && absdiff(a, p[-1]) < thr) | ((uint32_t)(x + 1 < vx && absdiff(a, p[1]) < thr) << 1)
+                | ((uint32_t)(y > 0 && absdiff(a, p[-C::RS]) < thr) << 2) | ((uint32_t)(y + 1 < vy && absdiff(a, p[C::RS]) < thr) << 3);
+    if (C::HZ) nb |= ((uint32_t)(z > 0 && absdiff(a, p[-C::PS]) < thr) << 4) | ((uint32_t)(z + 1 < vz && absdiff(a, p[C::PS]) < thr) << 5);
+    return nb;
 }
 
 /* Walk the component of voxel `start` on the staged bytes (6- or 4-connectivity inside the tile's
- * valid extent).  Returns false if it has more than WALK_MAX voxels; else root = smallest voxel
- * index, n = size, and the visited voxels are left in wq. */
+ * valid extent); nb = neighbour_mask(start).  Returns false if the component has more than WALK_MAX
+ * voxels; else root = smallest voxel index, n = size, and the visited voxels are left in wq. */
 template <class C>
-RG_FN bool walk_component(const uint8_t *img, int vx, int vy, int vz, int tmode, uint32_t t4, uint32_t start,
+RG_FN bool walk_component(const uint8_t *img, int vx, int vy, int vz, uint32_t thr, uint32_t start, uint32_t nb,
                           WalkQ &wq, int &n, uint32_t &root)
 {
     n = 1; root = start;
-    const int ndir = C::HZ ? 6 : 4;
-    {   /* most components are a single voxel: look at the start voxel's neighbours before paying for a queue */
-        const int x = (int)(start % C::TX), y = (int)((start / C::TX) % C::TY), z = (int)(start / (C::TX * C::TY));
-        const uint8_t *p = img + img_off<C>(x, y, z);
-        const uint32_t a = *p;
-        bool any = (x > 0 && similar1(a, p[-1], tmode, t4)) | (x + 1 < vx && similar1(a, p[1], tmode, t4))
-                 | (y > 0 && similar1(a, p[-C::RS], tmode, t4)) | (y + 1 < vy && similar1(a, p[C::RS], tmode, t4));
-        if (C::HZ) any = any | (z > 0 && similar1(a, p[-C::PS], tmode, t4)) | (z + 1 < vz && similar1(a, p[C::PS], tmode, t4));
-        if (!any) return true;
-    }
     wq_clear(wq);
     wq_set(wq, 0, start);
     int head = 0;
-    while (head < n) {
-        const uint32_t v = wq_get(wq, head++);
-        const int x = (int)(v % C::TX), y = (int)((v / C::TX) % C::TY), z = (int)(v / (C::TX * C::TY));
-        const uint8_t *p = img + img_off<C>(x, y, z);
-        const uint32_t a = *p;
-        for (int d = 0; d < ndir; d++) {
-            int off; uint32_t u; bool ok;
-            if (d == 0) { ok = x > 0; off = -1; u = v - 1; }
-            else if (d == 1) { ok = x + 1 < vx; off = 1; u = v + 1; }
-            else if (d == 2) { ok = y > 0; off = -C::RS; u = v - C::TX; }
-            else if (d == 3) { ok = y + 1 < vy; off = C::RS; u = v + C::TX; }
-            else if (d == 4) { ok = z > 0; off = -C::PS; u = v - C::TX * C::TY; }
-            else { ok = z + 1 < vz; off = C::PS; u = v + C::TX * C::TY; }
-            if (!ok || !similar1(a, p[off], tmode, t4)) continue;
-            if (wq_has(wq, u)) continue;
+    uint32_t v = start;
+    for (;;) {
+        while (nb) {                                                /* usually one bit */
+            const int d = ffs1(nb) - 1; nb &= nb - 1;
+            const int step = (d < 2) ? 1 : (d < 4) ? C::TX : C::TX * C::TY;
+            const uint32_t u = (d & 1) ? v + step : v - step;
+            if (wq_has(wq, u, n)) continue;
             if (n == WALK_MAX) return false;
             wq_set(wq, n++, u);
             if (u < root) root = u;
         }
+        if (++head >= n) break;
+        v = wq_get(wq, head);
+        nb = neighbour_mask<C>(img, vx, vy, vz, thr, v);
     }
     return true;
 }
@@ -165,7 +169,7 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint3
         if ((side ? !has_xp : !has_xm) || y >= vy || z >= vz) return;
         const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
         const uint32_t own = o[0], other = o[side ? 1 : -1];
-        if (similar1(own, other, tmode, t4)) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
+        if (absdiff(own, other) < P.thr) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
     });
 }
 
@@ -184,7 +188,7 @@ RG_FN void seed_range(const Params &P, uint32_t tile, uint32_t &lo_out, uint32_t
 template <class C, class Exec>
 RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C> &s)
 {
-    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    int tx, ty, tz; ex.template origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
     const int vx = (int)((P.nx - x0) < C::TX ? (P.nx - x0) : C::TX);
     const int vy = (int)((P.ny - y0) < C::TY ? (P.ny - y0) : C::TY);
@@ -192,10 +196,10 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
 
     if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
     ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
-    ex.pfor(C::NW, [&](int i) { s.openbits[i] = 0; s.seedbits[i] = 0; });
+    ex.pfor(C::NW / 4, [&](int i) { st128(&s.openbits[4 * i], u32x4{0, 0, 0, 0}); st128(&s.seedbits[4 * i], u32x4{0, 0, 0, 0}); });
     if (ex.tid() == 0) {
         uint32_t lo, hi; seed_range(P, tile, lo, hi);
-        s.scal[SC_SEED_LO] = lo; s.scal[SC_SEED_HI] = hi; s.scal[SC_OVERFLOW] = 0; s.scal[SC_COMPLEX] = 0; s.scal[SC_UNIFORM] = 0;
+        s.scal[SC_SEED_LO] = lo; s.scal[SC_SEED_HI] = hi; s.scal[SC_OVERFLOW] = 0; s.scal[SC_COMPLEX] = 0; s.scal[SC_UNIFORM] = 0; s.scal[SC_NSLOW] = 0;
     }
     ex.tile_wait(&s.mbar);
     ex.sync();
@@ -204,7 +208,11 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     if (P.fast16 && P.tmode >= 1) {
         const uint32_t pat = (uint32_t)s.img[img_off<C>(0, 0, 0)] * 0x01010101u;
         bool differs = false;
-        ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+        {   /* cheap pre-test on the first row: almost every non-solid tile stops here */
+            u32x4 q = ld128(&s.img[img_off<C>(0, 0, 0)]);
+            differs = vx >= 16 && (((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) != 0);
+        }
+        if (!differs) ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
             int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
             if (y >= vy || z >= vz || 16 * c >= vx) return;
             u32x4 q = ld128(&s.img[img_off<C>(16 * c, y, z)]);
@@ -243,21 +251,35 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vz); }
     });
     ex.sync();
-    /* ... then one walk per edge, one thread each */
+    /* ... then one thread per edge.  Most start voxels have no similar neighbour inside the tile and are
+       their own component; the others go to a compact list so that the longer walks fill whole warps. */
+    uint16_t *slow = s.wprefix;                                     /* free until emit_nodes */
     ex.pfor((int)etot, [&](int e) {
-        WalkQ wq; int n; uint32_t root;
-        if (!walk_component<C>(s.img, vx, vy, vz, P.tmode, P.t4, s.ent_root[e], wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
-        atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
-        s.ent_root[e] = (uint16_t)root;
+        const uint32_t v = s.ent_root[e];
+        if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) {
+            uint32_t k = atomic_add(&s.scal[SC_NSLOW], 1u);
+            if (k < (uint32_t)C::NW) slow[k] = (uint16_t)e; else s.scal[SC_COMPLEX] = 1;
+        } else atomic_or(&s.openbits[v >> 5], 1u << (v & 31));
     });
-    /* ... and per seed */
     {
         const int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
         ex.pfor(hi - lo, [&](int i) {
+            const uint32_t v = (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu);
             WalkQ wq; int n; uint32_t root;
-            if (!walk_component<C>(s.img, vx, vy, vz, P.tmode, P.t4, (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
             atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
             atomic_or(&s.seedbits[root >> 5], 1u << (root & 31));
+        });
+    }
+    ex.sync();
+    if (!s.scal[SC_COMPLEX]) {
+        ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
+            const int e = slow[i];
+            const uint32_t v = s.ent_root[e];
+            WalkQ wq; int n; uint32_t root;
+            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
+            s.ent_root[e] = (uint16_t)root;
         });
     }
     ex.sync();
@@ -283,7 +305,7 @@ RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
 template <class C, class Exec>
 RG_FN void flag_tile(Exec &ex, const Params &P, uint32_t tile)
 {
-    int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+    int tx, ty, tz; ex.template origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
     const TileRec rc = P.rec[tile];
     bool mine = false;

@@ -36,6 +36,7 @@ RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
     uint32_t m = __vcmpltu4(__vabsdiffu4(a, b), t4);          /* 0xFF per similar byte */
     return ((m & 0x01010101u) * 0x01020408u) >> 24;           /* gather the 4 flags into bits 0..3 */
 }
+RG_FN uint32_t absdiff(uint32_t a, uint32_t b) { return __sad((int)a, (int)b, 0u); }
 RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { return atomicOr(p, v); }
 RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
 RG_FN uint32_t atomic_max(uint32_t *p, uint32_t v) { return atomicMax(p, v); }
@@ -92,6 +93,7 @@ RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
     }
     return r;
 }
+RG_FN uint32_t absdiff(uint32_t a, uint32_t b) { return a > b ? a - b : b - a; }
 RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o | v; return o; }
 RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o + v; return o; }
 RG_FN uint32_t atomic_max(uint32_t *p, uint32_t v) { uint32_t o = *p; if (v > o) *p = v; return o; }

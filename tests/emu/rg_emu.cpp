@@ -27,6 +27,7 @@ struct HostExec {
     bool sync_or(bool p) { return p; }
     template <class C> bool tma_tile(const Params &, uint8_t *, uint64_t *, int64_t, int64_t, int64_t) { return false; }
     void tile_wait(uint64_t *) {}
+    template <class C> void origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz) const { tile_origin<C>(P, tile, tx, ty, tz); }
     uint32_t bid() const { return 0; }
     uint32_t nblk() const { return 1; }
     template <class F> uint32_t scan16(int n, F count, uint16_t *out, uint32_t *)
@@ -60,7 +61,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.image = image; P.mask = mask; P.nx = nx; P.ny = ny; P.nz = nz;
     P.ntx = (int)((nx + C::TX - 1) / C::TX); P.nty = (int)((ny + C::TY - 1) / C::TY); P.ntz = (int)((nz + C::TZ - 1) / C::TZ);
     P.zlo_ext = zlo; P.zhi_ext = zhi;
-    P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u;
+    P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
     size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
     size_t cap = 1 + ntiles * C::ENT_MAX + (size_t)nseeds;
