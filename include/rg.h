@@ -77,6 +77,25 @@ int rg_ctx_reserve(rg_ctx *ctx, int64_t nx, int64_t ny, int64_t nz, int nseeds);
 int rg_grow_device(rg_ctx *ctx, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
                    const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream);
 
+/* No counterpart in the reference (its growers cudaMalloc and cudaFree on every call, raycast.cu:711-713,
+ * 751-753).  Same computation and same arguments as rg_grow_device, for callers that must not allocate
+ * device memory while they run -- a host that gave the whole card to its own pool at start-up, a
+ * latency-critical loop that cannot take cudaMalloc's device-wide synchronisation or a late out-of-memory
+ * error, a plugin with a fixed footprint.  No context: all engine scratch is one 64 MiB array built into the
+ * library (rg_noalloc_scratch_bytes()), resident on every GPU that loads the library until the process
+ * exits.  The call allocates and frees nothing, on the host or the device.
+ *   - Limits: rg_workspace_bytes(nx, ny, nz, nseeds) <= 64 MiB (for instance 256 x 256 x 512 voxels, or a
+ *     8192 x 8192 image) and nseeds <= 2048; anything larger returns RG_ERR_TOO_LARGE with a message.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress) and sets
+ *     the kernels' shared-memory attributes; make that first call before any stream capture begins.
+ *   - All calls on a device share the array.  Calls whose GPU work can overlap (two streams, two host
+ *     threads) corrupt each other: issue them back to back on one stream, or serialise them yourself.
+ *     Nothing carries over between calls: each call's first kernel resets the counters it relies on.
+ * d_image, d_seeds_xyz, d_mask are device pointers on the current device; work is enqueued on `stream`. */
+int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+                           const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream);
+int64_t rg_noalloc_scratch_bytes(void);
+
 /* Synchronises the stream last used and returns RG_OK or RG_ERR_INTERNAL / RG_ERR_CUDA;
  * stats (may be NULL) receives {coarse nodes, status bits, tiles labelled by the full pass, tiles holding region voxels}. */
 int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);

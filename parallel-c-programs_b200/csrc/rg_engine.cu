@@ -717,3 +717,67 @@ extern "C" int rg_grow_region_2d(unsigned char *image, int width, int height, un
     const int32_t seeds[12] = { 4, 4, 0, width - 6, 4, 0, width - 6, height - 6, 0, 4, height - 6, 0 };
     return grow_host(image, width, height, 1, seeds, 4, 2 /* region.c:81 */, mask_out, apply ? image : nullptr);
 }
+
+/* ------------------------------------------------------------------ grow without any allocation
+ *
+ * Some hosts may not allocate device memory once they are running: an application that has handed the
+ * whole card to its own memory pool at start-up and refuses later driver allocations, a service on a
+ * latency-critical path that cannot afford cudaMalloc's implicit device-wide synchronisation or a late
+ * out-of-memory failure, a plugin that must keep a fixed footprint.  For them this entry point runs the
+ * same kernels as rg_grow_device, but every byte of engine scratch (tile records, face lists, coarse
+ * union-find, work lists, seed keys) lives in ONE array that is part of the library image, so nothing is
+ * allocated, freed or grown -- not here and not in any routine it calls.
+ *
+ * The price: the array has a fixed size (RG_NOALLOC_SCRATCH_BYTES, 64 MiB), it occupies that much memory on
+ * every GPU that loads the library until the process exits, and every call on a device uses the same
+ * array.  Two calls whose GPU work overlaps (different streams, different host threads) would overwrite
+ * each other's scratch: run them one after the other.  The array keeps whatever the previous call left
+ * in it; the first kernel of each call resets the counters and the "holds a seed" node, and everything
+ * else is written before it is read, so no call depends on the previous one.
+ */
+#define RG_NOALLOC_SCRATCH_BYTES (64u << 20)
+#define RG_NOALLOC_MAX_SEEDS 2048
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RG_NOALLOC_SCRATCH_BYTES];
+/* `g_noalloc_scratch` names a device object; in host code it is only a handle.  The address the kernels
+   need is looked up once per device, with that device current, and kept here. */
+static void *g_noalloc_addr[64];
+static bool g_noalloc_attr[64];
+
+extern "C" int64_t rg_noalloc_scratch_bytes(void) { return (int64_t)RG_NOALLOC_SCRATCH_BYTES; }
+
+extern "C" int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
+                                      const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream)
+{
+    if (!d_image || !d_mask || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !d_seeds_xyz))
+        return fail(RG_ERR_ARG, "bad argument");
+    if (nseeds > RG_NOALLOC_MAX_SEEDS)
+        return fail(RG_ERR_TOO_LARGE, "rg_grow_device_noalloc takes at most 2048 seeds (larger lists need the sorting scratch of rg_grow_device)");
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    if (rc) return rc;
+    if (L.total > (size_t)RG_NOALLOC_SCRATCH_BYTES) {
+        snprintf(g_err, sizeof g_err, "rg_grow_device_noalloc: this size needs %zu bytes of scratch but the built-in scratch holds %u "
+                 "(64 MiB, e.g. up to 256x256x512 voxels); use rg_grow_device with a context instead", L.total, RG_NOALLOC_SCRATCH_BYTES);
+        return RG_ERR_TOO_LARGE;
+    }
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RG_ERR_ARG, "device index");
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (!g_noalloc_addr[dev]) {                         /* first call on this device */
+            void *p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            if (!p) return fail(RG_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+            g_noalloc_addr[dev] = p;
+        }
+    }
+    rg_ctx view;                                            /* a view of the built-in scratch; owns nothing */
+    memset(&view, 0, sizeof view);
+    view.device = dev;
+    view.ws = g_noalloc_addr[dev];
+    view.ws_bytes = RG_NOALLOC_SCRATCH_BYTES;
+    view.attr_set = g_noalloc_attr[dev];
+    rc = grow_device_impl(&view, d_image, nx, ny, nz, 0, 0, d_seeds_xyz, nseeds, threshold, d_mask, stream);
+    g_noalloc_attr[dev] = view.attr_set;
+    return rc;
+}
