@@ -1,0 +1,60 @@
+#!/usr/bin/env python3
+"""Multi-GPU parity check (not a pytest file; run under torchrun on a box with >= 2 GPUs):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29700 tests/mgpu_check.py
+
+Every rank labels its z-slab with the CUDA engine, interface lists are all-gathered over NCCL, and the
+assembled mask is compared byte for byte with the oracle on rank 0 (C4 geometry: the z-serpentine crosses
+every slab interface 64 times; plus a random ragged volume)."""
+import ctypes, os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "parallel-c-programs_b200")); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import rgb200
+from conftest import Oracle
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    lib = rgb200.load_library()
+    ctx = rgb200.Context(local)
+    ora = Oracle()
+    cases = []
+    img, seeds, T = ora.synth("c4", 256, 0x5EED0004); cases.append(("c4-256", img, seeds, T))
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 3, size=(61, 70, 208), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 208, 8), rng.integers(0, 70, 8), rng.integers(0, 61, 8)], 1).astype(np.int32)
+    cases.append(("random-ragged", img, seeds, 1))
+    ok = True
+    for name, img, seeds, T in cases:
+        nz, ny, nx = img.shape
+        g = rgb200.SlabGrower(lib, ctx.handle, nx, ny, nz, rank, world, dev)
+        g.image.copy_(torch.from_numpy(img[g.z0:g.z1]).to(dev))
+        g.exchange_image_halos()
+        g.set_seeds(seeds)
+        m = g.grow(T)
+        torch.cuda.synchronize()
+        st = ctx.status()
+        parts = [torch.empty((rgb200.slab_bounds(nz, r, world)[1] - rgb200.slab_bounds(nz, r, world)[0], ny, nx), dtype=torch.uint8, device=dev)
+                 for r in range(world)]
+        dist.all_gather(parts, m.contiguous())
+        if rank == 0:
+            got = torch.cat(parts).cpu().numpy()
+            want = ora.grow(img, seeds, T)
+            same = bool((got == want).all())
+            ok = ok and same
+            print(f"{name}: world={world} parity={'OK' if same else 'MISMATCH'} region={int(want.sum())} status={st}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0 and not ok:
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()
