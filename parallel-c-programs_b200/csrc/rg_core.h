@@ -614,10 +614,12 @@ RG_FN void make_seed_keys(Exec &ex, const Params &P, const int32_t *seeds_xyz, u
 }
 
 /* resets the per-call counters; node 0 is the "holds a seed" super node */
+enum { FAST_NODE_SLOTS = 1024 };    /* node ids 1 + tile * 1024 .. belong to the tile's fast pass (rg_fast.h) */
 RG_FN void reset_counters(const Params &P)
 {
     for (int i = 0; i < CTR_WORDS; i++) P.counters[i] = 0;
-    P.counters[CTR_NODES] = 1;
+    /* node 0, then one fixed block per tile for the fast pass; the full pass allocates behind them */
+    P.counters[CTR_NODES] = 1u + (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz * (uint32_t)FAST_NODE_SLOTS;
     P.nparent[0] = 0;
 }
 

@@ -323,7 +323,7 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
 {
     int64_t ntx = (nx + C::TX - 1) / C::TX, nty = (ny + C::TY - 1) / C::TY, ntz = (nz + C::TZ - 1) / C::TZ;
     int64_t ntiles = ntx * nty * ntz;
-    int64_t node_cap = 1 + ntiles * (int64_t)C::ENT_MAX + (int64_t)nseeds;
+    int64_t node_cap = 1 + ntiles * ((int64_t)C::ENT_MAX + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
     if (ntiles >= (1ll << 31) || node_cap >= (1ll << 32)) return fail(RG_ERR_TOO_LARGE, "volume too large for 32-bit node ids");
     L.ntx = (int)ntx; L.nty = (int)nty; L.ntz = (int)ntz; L.ntiles = (uint32_t)ntiles; L.node_cap = (uint32_t)node_cap;
     size_t o = 0;

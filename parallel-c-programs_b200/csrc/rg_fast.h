@@ -27,7 +27,9 @@
 namespace rg {
 
 enum { WALK_MAX = 16 };                       /* voxels a walk may visit before the tile is called complex */
-enum { FAST_ENT_MAX = 2048 };                 /* face-list entries the fast pass keeps per tile */
+enum { FAST_ENT_MAX = 768 };                  /* cross-tile edges a non-uniform tile may have on the fast path */
+enum { HASH_BITS = 10, HASH_N = 1 << HASH_BITS, HASH_MAX_KEYS = 704 };
+static_assert((int)HASH_N == (int)FAST_NODE_SLOTS, "one node slot per hash slot");   /* representative -> dense node id */
 
 template <class C>
 struct alignas(128) FastSmem {
@@ -35,14 +37,38 @@ struct alignas(128) FastSmem {
     uint64_t mbar;
     uint32_t fmask[C::FW_TOTAL];
     uint16_t fprefix[C::FW_TOTAL + 2];
-    uint16_t ent_root[FAST_ENT_MAX];
-    alignas(16) uint32_t openbits[C::NW];
-    alignas(16) uint32_t seedbits[C::NW];
-    uint16_t wprefix[C::NW];
+    uint16_t ent_root[FAST_ENT_MAX];              /* per edge: start voxel, later the hash slot of its component */
+    uint16_t slow[FAST_ENT_MAX];                  /* edges whose start voxel has a similar neighbour inside the tile */
+    alignas(16) uint32_t tab[HASH_N];             /* open addressing: (representative + 1) << 16 | node id, 0 = empty */
+    alignas(16) uint32_t seedtab[HASH_N / 32];    /* bit per slot: the component holds a seed */
     uint32_t scal[16];
     uint32_t scan_scratch[40];
     static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit");
 };
+
+/* find or insert representative `root`; the inserting thread hands out the next dense id.  Ids are read
+   back only after a barrier, so nobody waits on the short window in which a slot is claimed but unnumbered. */
+RG_FN uint32_t hash_slot(uint32_t *tab, uint32_t *scal, uint32_t root)
+{
+    const uint32_t key = (root + 1u) << 16;
+    uint32_t slot = (root * 2654435761u) >> (32 - HASH_BITS);
+    for (int probe = 0; probe < HASH_N; probe++) {
+        uint32_t cur = ldv32(&tab[slot]);
+        if (cur == 0u) {
+            cur = cas32(&tab[slot], 0u, key | 0xFFFFu);
+            if (cur == 0u) {
+                uint32_t id = atomic_add(&scal[SC_NNODES], 1u);
+                if (id >= (uint32_t)HASH_MAX_KEYS) { scal[SC_COMPLEX] = 1; id = 0; }
+                stv32(&tab[slot], key | id);
+                return slot;
+            }
+        }
+        if ((cur >> 16) == root + 1u) return slot;
+        slot = (slot + 1u) & (HASH_N - 1);
+    }
+    scal[SC_COMPLEX] = 1;
+    return 0;
+}
 
 /* ---- a tiny queue of 16-bit entries packed in four 64-bit registers ---- */
 struct WalkQ { uint64_t a, b, c, d; };
@@ -185,6 +211,14 @@ RG_FN void seed_range(const Params &P, uint32_t tile, uint32_t &lo_out, uint32_t
 }
 
 /* ================================================================ fast labelling pass */
+RG_FN uint32_t fast_node_base(uint32_t tile) { return 1u + tile * (uint32_t)HASH_N; }   /* fixed slots: no global atomic */
+
+template <class C, class Exec>
+RG_FN void fast_give_up(Exec &ex, const Params &P, uint32_t tile)
+{
+    if (ex.tid() == 0) P.complex_list[atomic_add(&P.counters[CTR_NCOMPLEX], 1u)] = tile;
+}
+
 template <class C, class Exec>
 RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C> &s)
 {
@@ -196,10 +230,11 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
 
     if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
     ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
-    ex.pfor(C::NW / 4, [&](int i) { st128(&s.openbits[4 * i], u32x4{0, 0, 0, 0}); st128(&s.seedbits[4 * i], u32x4{0, 0, 0, 0}); });
+    ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
+    ex.pfor(HASH_N / 32, [&](int i) { s.seedtab[i] = 0; });
     if (ex.tid() == 0) {
         uint32_t lo, hi; seed_range(P, tile, lo, hi);
-        s.scal[SC_SEED_LO] = lo; s.scal[SC_SEED_HI] = hi; s.scal[SC_OVERFLOW] = 0; s.scal[SC_COMPLEX] = 0; s.scal[SC_UNIFORM] = 0; s.scal[SC_NSLOW] = 0;
+        s.scal[SC_SEED_LO] = lo; s.scal[SC_SEED_HI] = hi; s.scal[SC_NNODES] = 0; s.scal[SC_COMPLEX] = 0; s.scal[SC_NSLOW] = 0;
     }
     ex.tile_wait(&s.mbar);
     ex.sync();
@@ -207,87 +242,88 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     bool uniform = false;
     if (P.fast16 && P.tmode >= 1) {
         const uint32_t pat = (uint32_t)s.img[img_off<C>(0, 0, 0)] * 0x01010101u;
-        bool differs = false;
-        {   /* cheap pre-test on the first row: almost every non-solid tile stops here */
-            u32x4 q = ld128(&s.img[img_off<C>(0, 0, 0)]);
-            differs = vx >= 16 && (((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) != 0);
+        u32x4 q0 = ld128(&s.img[img_off<C>(0, 0, 0)]);
+        /* the first 16 voxels decide for almost every tile; all threads read the same bytes, so this branch is uniform */
+        if (vx >= 16 && ((q0.x ^ pat) | (q0.y ^ pat) | (q0.z ^ pat) | (q0.w ^ pat)) == 0u) {
+            bool differs = false;
+            ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+                int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+                if (y >= vy || z >= vz || 16 * c >= vx) return;
+                u32x4 q = ld128(&s.img[img_off<C>(16 * c, y, z)]);
+                if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) differs = true;
+            });
+            uniform = !ex.sync_or(differs);
         }
-        if (!differs) ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
-            int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
-            if (y >= vy || z >= vz || 16 * c >= vx) return;
-            u32x4 q = ld128(&s.img[img_off<C>(16 * c, y, z)]);
-            if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) differs = true;
-        });
-        uniform = !ex.sync_or(differs);
     }
     build_face_masks<C>(ex, P, s.img, s.fmask, x0, y0, z0);
     ex.sync();
-    uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
-    if (ex.tid() == 0) { s.fprefix[C::FW_TOTAL] = (uint16_t)etot; s.scal[SC_ETOT] = etot; }
-    ex.sync();
-    if (etot > FAST_ENT_MAX) {                                      /* uniform: every thread sees the same total */
-        if (ex.tid() == 0) P.complex_list[atomic_add(&P.counters[CTR_NCOMPLEX], 1u)] = tile;
-        return;
-    }
+    const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
+    if (ex.tid() == 0) s.fprefix[C::FW_TOTAL] = (uint16_t)etot;
+    const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
+    const uint32_t base = fast_node_base(tile);
+    uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
+    uint32_t nnodes;
     if (uniform) {
-        const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
-        ex.pfor((int)etot, [&](int e) { s.ent_root[e] = 0; });
-        if (ex.tid() == 0) {
-            if (etot || seeded) s.openbits[0] = 1u;
-            if (seeded) s.seedbits[0] = 1u;
-            s.scal[SC_UNIFORM] = 1;
+        ex.pfor((int)etot, [&](int e) { ent[e] = 0; });
+        nnodes = (etot || seeded) ? 1u : 0u;
+        if (ex.tid() == 0 && nnodes) { P.nparent[base] = seeded ? 0u : base; P.nrep[base] = 0; }
+    } else {
+        if (etot > (uint32_t)FAST_ENT_MAX) { fast_give_up<C>(ex, P, tile); return; }     /* same total in every thread */
+        /* start voxel of every cross-tile edge, in list order ... */
+        ex.pfor(C::FW_TOTAL, [&](int fw) {
+            uint32_t m = s.fmask[fw];
+            if (!m) return;
+            int f = 0; while (fw >= C::fw_off(f + 1)) f++;
+            const int idx = fw - C::fw_off(f);
+            uint32_t slot = s.fprefix[fw];
+            while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vz); }
+        });
+        ex.sync();
+        /* ... then one thread per edge.  Most start voxels have no similar neighbour inside the tile and are their
+           own component; the others go to a compact list so that the longer walks fill whole warps. */
+        ex.pfor((int)etot, [&](int e) {
+            const uint32_t v = s.ent_root[e];
+            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
+            else s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, v);
+        });
+        {
+            const int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
+            ex.pfor(hi - lo, [&](int i) {
+                const uint32_t v = (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu);
+                WalkQ wq; int n; uint32_t root;
+                if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+                const uint32_t slot = hash_slot(s.tab, s.scal, root);
+                atomic_or(&s.seedtab[slot >> 5], 1u << (slot & 31));
+            });
         }
         ex.sync();
-        emit_nodes<C>(ex, P, tile, s);
-        return;
-    }
-    /* start voxel of every cross-tile edge, in list order ... */
-    ex.pfor(C::FW_TOTAL, [&](int fw) {
-        uint32_t m = s.fmask[fw];
-        if (!m) return;
-        int f = 0; while (fw >= C::fw_off(f + 1)) f++;
-        const int idx = fw - C::fw_off(f);
-        uint32_t slot = s.fprefix[fw];
-        while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vz); }
-    });
-    ex.sync();
-    /* ... then one thread per edge.  Most start voxels have no similar neighbour inside the tile and are
-       their own component; the others go to a compact list so that the longer walks fill whole warps. */
-    uint16_t *slow = s.wprefix;                                     /* free until emit_nodes */
-    ex.pfor((int)etot, [&](int e) {
-        const uint32_t v = s.ent_root[e];
-        if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) {
-            uint32_t k = atomic_add(&s.scal[SC_NSLOW], 1u);
-            if (k < (uint32_t)C::NW) slow[k] = (uint16_t)e; else s.scal[SC_COMPLEX] = 1;
-        } else atomic_or(&s.openbits[v >> 5], 1u << (v & 31));
-    });
-    {
-        const int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
-        ex.pfor(hi - lo, [&](int i) {
-            const uint32_t v = (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu);
-            WalkQ wq; int n; uint32_t root;
-            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
-            atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
-            atomic_or(&s.seedbits[root >> 5], 1u << (root & 31));
-        });
-    }
-    ex.sync();
-    if (!s.scal[SC_COMPLEX]) {
         ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
-            const int e = slow[i];
+            const int e = s.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
             if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
-            atomic_or(&s.openbits[root >> 5], 1u << (root & 31));
-            s.ent_root[e] = (uint16_t)root;
+            s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, root);
+        });
+        ex.sync();
+        if (s.scal[SC_COMPLEX]) { fast_give_up<C>(ex, P, tile); return; }
+        nnodes = s.scal[SC_NNODES];
+        /* node ids are final now: face lists and nodes go out in one sweep */
+        ex.pfor((int)etot, [&](int e) { ent[e] = (uint16_t)(s.tab[s.ent_root[e]] & 0xFFFFu); });
+        ex.pfor(HASH_N, [&](int slot) {
+            const uint32_t cur = s.tab[slot];
+            if (!cur) return;
+            const uint32_t g = base + (cur & 0xFFFFu);
+            P.nparent[g] = ((s.seedtab[slot >> 5] >> (slot & 31)) & 1u) ? 0u : g;      /* seeded components start hooked to node 0 */
+            P.nrep[g] = (uint16_t)((cur >> 16) - 1u);
         });
     }
-    ex.sync();
-    if (s.scal[SC_COMPLEX]) {
-        if (ex.tid() == 0) P.complex_list[atomic_add(&P.counters[CTR_NCOMPLEX], 1u)] = tile;
-        return;
+    if (ex.tid() == 0) {
+        TileRec rc;
+        rc.node_base = base; rc.nnodes = nnodes;
+        for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]);
+        rc.uniform = uniform ? 1 : 0; rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
+        P.rec[tile] = rc;
     }
-    emit_nodes<C>(ex, P, tile, s);
 }
 
 /* the full pass over the tiles the fast pass gave up on (persistent CTAs) */

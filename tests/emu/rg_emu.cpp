@@ -64,7 +64,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
     size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
-    size_t cap = 1 + ntiles * C::ENT_MAX + (size_t)nseeds;
+    size_t cap = 1 + ntiles * ((size_t)C::ENT_MAX + FAST_NODE_SLOTS) + (size_t)nseeds;
     E.rec.assign(ntiles, TileRec()); E.ent.assign(ntiles * C::ENT_MAX, 0); E.npar.assign(cap, 0xDEADBEEF); E.nrep.assign(cap, 0);
     E.keys.assign((size_t)std::max(nseeds, 1), ~0ull);
     E.clist.assign(ntiles, 0); E.flist.assign(ntiles, 0);
@@ -109,7 +109,8 @@ static int emu_grow_t(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, 
     emu_setup<C>(E, image, nx, ny, nz, 0, 0, seeds, nseeds, T, mask);
     emu_label<C>(E);
     emu_finish<C>(E);
-    if (stats) { stats[0] = E.counters[CTR_NODES]; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX]; stats[3] = (uint32_t)E.rec.size(); }
+    uint32_t real_nodes = 0; for (const TileRec &r : E.rec) real_nodes += r.nnodes;
+    if (stats) { stats[0] = real_nodes; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX]; stats[3] = (uint32_t)E.rec.size(); }
     return E.counters[CTR_STATUS] ? -4 : 0;
 }
 
