@@ -66,7 +66,12 @@ struct TileCfg {
 };
 
 /* tile shapes: ~32 K voxels either way.  2-D: 254 rows so that the staged tile (256 rows) is one TMA box */
-typedef TileCfg<64, 32, 16> Cfg3D;
+#ifndef RG_TX3
+#define RG_TX3 64
+#define RG_TY3 32
+#define RG_TZ3 16
+#endif
+typedef TileCfg<RG_TX3, RG_TY3, RG_TZ3> Cfg3D;
 typedef TileCfg<128, 254, 1> Cfg2D;
 
 struct TileRec {                 /* 32 bytes per tile, written by pass A */
@@ -99,6 +104,7 @@ struct Params {
     uint32_t node_cap;
     uint32_t *complex_list;      /* tiles the fast labelling pass handed to the full one */
     uint32_t *flag_list;         /* tiles that hold part of the region (pass C work list) */
+    int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
 /* ---------------------------------------------------------------- shared-memory tile state */

@@ -125,7 +125,9 @@ struct DevExec {
 
 /* ------------------------------------------------------------------ kernels */
 #define RG_THREADS 512          /* full tile passes: 2 CTAs/SM (105 KB smem each) */
-#define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (56 KB smem each) */
+#ifndef RG_FAST_THREADS
+#define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (68 KB smem each) */
+#endif
 #define RG_FLAG_THREADS 128     /* flag / zero-fill: no smem */
 #define RG_PERSISTENT_CTAS (148 * 2)
 
@@ -434,6 +436,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.thr = threshold <= 0 ? 0u : threshold >= 256 ? 256u : (uint32_t)threshold;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
     P.nseeds = nseeds;
+    { static int dbg = -1; if (dbg < 0) { const char *e = getenv("RG_DEBUG_STOP"); dbg = e ? atoi(e) : 0; } P.debug_stop = dbg; }
     memset(&c->last_tmap, 0, sizeof c->last_tmap);
     P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, d_image - (size_t)zlo_ext * nx * ny, nx, ny, nz + zlo_ext + zhi_ext)) ? 1 : 0;
     P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
@@ -458,11 +461,11 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     const dim3 tile_grid = g3 ? dim3((unsigned)L.ntx, (unsigned)L.nty, (unsigned)L.ntz) : dim3(L.ntiles, 1, 1);
     c->last_grid = tile_grid;
     k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
-    k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
+    if (!P.debug_stop) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
     int64_t items = (int64_t)L.ntiles * 3;
     int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
-    k_merge<C><<<mb, 256, 0, st>>>(P);
+    if (!P.debug_stop) k_merge<C><<<mb, 256, 0, st>>>(P);
     if (c->profile) cudaEventRecord(c->ev[3], st);
     CK(cudaGetLastError());
     c->last_counters = P.counters; c->last_stream = st;
@@ -474,6 +477,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
 static int launch_finish(rg_ctx *c, cudaStream_t st)
 {
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
+    if (c->last_P.debug_stop) { if (c->profile) cudaEventRecord(c->ev[4], st); return RG_OK; }   /* tuning runs time the fast pass only */
     if (c->last_is2d) {
         k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
         k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);

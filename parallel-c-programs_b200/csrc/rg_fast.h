@@ -238,6 +238,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     }
     ex.tile_wait(&s.mbar);
     ex.sync();
+    if (P.debug_stop == 1) return;
     /* a tile whose own voxels are all equal is one component with representative 0 (solid interiors) */
     bool uniform = false;
     if (P.fast16 && P.tmode >= 1) {
@@ -257,6 +258,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     }
     build_face_masks<C>(ex, P, s.img, s.fmask, x0, y0, z0);
     ex.sync();
+    if (P.debug_stop == 3) return;
     const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
     if (ex.tid() == 0) s.fprefix[C::FW_TOTAL] = (uint16_t)etot;
     const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
@@ -297,6 +299,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             });
         }
         ex.sync();
+        if (P.debug_stop == 6) return;
         ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
             const int e = s.slow[i];
             const uint32_t v = s.ent_root[e];
@@ -305,6 +308,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, root);
         });
         ex.sync();
+        if (P.debug_stop == 7) return;
         if (s.scal[SC_COMPLEX]) { fast_give_up<C>(ex, P, tile); return; }
         nnodes = s.scal[SC_NNODES];
         /* node ids are final now: face lists and nodes go out in one sweep */

@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG_DIR, "libb200rg.so")
+LIB_PATH = os.environ.get("RG_LIB") or os.path.join(_PKG_DIR, "libb200rg.so")   # RG_LIB: tuning experiments only
 
 RG_OK = 0
 _c = ctypes
