@@ -358,7 +358,7 @@ def main():
                    "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (no flush needed)" if main_res["nvox"] > 4e8 else "input+output ~2x L2; no flush",
                    "check": main_res["check"], "region_voxels": main_res["region_voxels"], "coarse_nodes": main_res["nodes"],
-                   "tiles": {"total": -(-n // 64) * -(-n // 32) * -(-n // 16) if WORKLOADS[wl][2] == 3 else -(-n // 128) * -(-n // 254),
+                   "tiles": {"total": -(-n // 64) * -(-n // 32) * -(-n // 16) if WORKLOADS[wl][2] == 3 else -(-n // 128) * -(-n // 126),
                              "full_label_pass": main_res["complex_tiles"], "with_region": main_res["region_tiles"]}},
         "gpu_launches": main_res["launches"] * args.steps,
         "clocks": main_res.get("clocks"),

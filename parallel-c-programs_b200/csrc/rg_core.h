@@ -65,14 +65,17 @@ struct TileCfg {
     }
 };
 
-/* tile shapes: ~32 K voxels either way.  2-D: 254 rows so that the staged tile (256 rows) is one TMA box */
+/* tile shapes: ~32 K voxels either way.  2-D: 126 rows (staged tile = 128 rows, one TMA box; the flood of pass C advances one row per sweep) */
 #ifndef RG_TX3
 #define RG_TX3 64
 #define RG_TY3 32
 #define RG_TZ3 16
 #endif
 typedef TileCfg<RG_TX3, RG_TY3, RG_TZ3> Cfg3D;
-typedef TileCfg<128, 254, 1> Cfg2D;
+#ifndef RG_TY2
+#define RG_TY2 126
+#endif
+typedef TileCfg<128, RG_TY2, 1> Cfg2D;
 
 struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint32_t node_base;          /* first global node id of this tile */
@@ -267,7 +270,8 @@ RG_FN void load_tile(Exec &ex, const Params &P, uint8_t *img, int64_t x0, int64_
 
 /* ---------------------------------------------------------------- edge bit planes (+ face masks if FACES) */
 template <class C, bool FACES, class Exec>
-RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, int64_t y0, int64_t z0)
+RG_FN void build_edges(Exec &ex, const Params &P, const uint8_t *img, uint32_t *pex, uint32_t *pey, uint32_t *pez, uint32_t *fmask,
+                        int64_t x0, int64_t y0, int64_t z0)
 {
     const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
     const int tmode = P.tmode; const uint32_t t4 = P.t4;
@@ -282,7 +286,7 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
         uint32_t vmask = (y < vy && z < vz) ? valid_bits(nx - gx0) : 0u;
         uint32_t exw = 0, eyw = 0, ezw = 0;
         if (vmask) {
-            const uint8_t *rowp = &s.u.i.img[img_off<C>(32 * wx, y, z)];
+            const uint8_t *rowp = &img[img_off<C>(32 * wx, y, z)];
             uint32_t a[8], b[8];
             load8(rowp, a);
             /* +x */
@@ -293,13 +297,13 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
             uint32_t nextvalid = (gx0 + 32 < nx) ? 0x80000000u : 0u;
             uint32_t e = edge_word(a, b, tmode, t4) & vmask & ((vmask >> 1) | nextvalid);
             if (wx == C::WX - 1) {
-                if (FACES && (e >> 31)) { int bi = z * C::TY + y; atomic_or(&s.fmask[C::fw_off(F_XP) + (bi >> 5)], 1u << (bi & 31)); }
+                if (FACES && (e >> 31)) { int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XP) + (bi >> 5)], 1u << (bi & 31)); }
                 e &= 0x7FFFFFFFu;
             }
             exw = e;
             if (FACES && wx == 0 && x0 > 0 && (vmask & 1u)) {
                 if (similar1(rowp[-1], a[0] & 0xFFu, tmode, t4)) {
-                    int bi = z * C::TY + y; atomic_or(&s.fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31));
+                    int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31));
                 }
             }
             /* +y */
@@ -309,12 +313,12 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
             } else if (FACES && has_yp) {                       /* y == TY-1: edges into the +y tile */
                 load8(rowp + C::RS, b);
                 uint32_t m = edge_word(a, b, tmode, t4) & vmask;
-                s.fmask[C::fw_off(F_YP) + z * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
+                fmask[C::fw_off(F_YP) + z * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
             }
             if (FACES && y == 0 && has_ym) {
                 load8(rowp - C::RS, b);
                 uint32_t m = edge_word(b, a, tmode, t4) & vmask;
-                s.fmask[C::fw_off(F_YM) + z * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
+                fmask[C::fw_off(F_YM) + z * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
             }
             /* +z */
             if (C::HZ) {
@@ -325,16 +329,16 @@ RG_FN void build_edges(Exec &ex, const Params &P, TileSmem<C> &s, int64_t x0, in
                 } else if (FACES && has_zp) {                   /* top valid plane: edges into the +z tile / slab */
                     load8(rowp + zs, b);
                     uint32_t m = edge_word(a, b, tmode, t4) & vmask;
-                    s.fmask[C::fw_off(F_ZP) + y * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
+                    fmask[C::fw_off(F_ZP) + y * C::WX + wx] = dedupe(m, e, xedges_within(b, tmode, t4));
                 }
                 if (FACES && z == 0 && has_zm) {
                     load8(rowp - zs, b);
                     uint32_t m = edge_word(b, a, tmode, t4) & vmask;
-                    s.fmask[C::fw_off(F_ZM) + y * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
+                    fmask[C::fw_off(F_ZM) + y * C::WX + wx] = dedupe(m, xedges_within(b, tmode, t4), e);
                 }
             }
         }
-        s.ex[w] = exw; s.ey[w] = eyw; s.ez[w] = ezw;
+        pex[w] = exw; pey[w] = eyw; pez[w] = ezw;
     });
 }
 
@@ -436,7 +440,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
     ex.tile_wait(&s.mbar);
     ex.sync();
-    build_edges<C, true>(ex, P, s, x0, y0, z0);
+    build_edges<C, true>(ex, P, s.u.i.img, s.ex, s.ey, s.ez, s.fmask, x0, y0, z0);
     ex.sync();
     label_runs<C>(ex, s);
 
@@ -445,7 +449,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     if (ex.tid() == 0) { s.fprefix[C::FW_TOTAL] = (uint16_t)etot; s.scal[SC_ETOT] = etot; }
     ex.sync();
 
-    /* roots of every component that owns a cross-tile edge ... */
+    /* start voxel of every cross-tile edge, in list order ... */
     ex.pfor(C::FW_TOTAL, [&](int fw) {
         uint32_t m = s.fmask[fw];
         if (!m) return;
@@ -458,11 +462,17 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
             if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
             else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? C::TY - 1 : 0; }
             else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
-            int w = (z * C::TY + y) * C::WX + (x >> 5);
-            uint32_t r = find16(s.u.parent, run_start(s.ex[w], w, x & 31));
-            atomic_or(&s.openbits[r >> 5], 1u << (r & 31));
-            s.ent_root[slot++] = (uint16_t)r;
+            s.ent_root[slot++] = (uint16_t)((z * C::TY + y) * C::TX + x);
         }
+    });
+    ex.sync();
+    /* ... then the root of each edge's component, one thread per edge (a face can hold 32 edges per word) */
+    ex.pfor((int)etot, [&](int e) {
+        const uint32_t v = s.ent_root[e];
+        const int w = (int)(v >> 5);
+        uint32_t r = find16(s.u.parent, run_start(s.ex[w], w, (int)(v & 31)));
+        atomic_or(&s.openbits[r >> 5], 1u << (r & 31));
+        s.ent_root[e] = (uint16_t)r;
     });
     /* ... or a seed */
     {
@@ -535,63 +545,92 @@ RG_FN void fill_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t 
 template <class C, class Exec>
 RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0) { fill_tile<C>(ex, P, x0, y0, z0, 0u); }
 
-template <class C, class Exec>
-RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
+/* shared memory of pass C: staged tile, edge planes, region bits */
+template <class C>
+struct alignas(128) FloodSmem {
+    uint8_t img[C::IMG_BYTES];
+    uint64_t mbar;
+    alignas(16) uint32_t ex[C::NW];
+    alignas(16) uint32_t ey[C::NW];
+    alignas(16) uint32_t ez[C::NW];
+    alignas(16) uint32_t M[C::NW];                 /* bit i: voxel i is in the region */
+    uint32_t scal[16];
+};
+
+/* all voxels reachable from the set bits of s along the links of A (bit i: voxel i linked to i+1), inside
+   one 32-voxel word: a carry runs from each seed to the end of its run (upwards), and the same on the
+   bit-reversed word (downwards) */
+RG_FN uint32_t fill_up(uint32_t s, uint32_t A) { return ((A + (s & A)) ^ A) | s; }
+#if RG_DEVICE_BUILD
+RG_FN uint32_t brev32(uint32_t x) { return __brev(x); }
+#else
+RG_FN uint32_t brev32(uint32_t x) { uint32_t r = 0; for (int i = 0; i < 32; i++) if ((x >> i) & 1u) r |= 1u << (31 - i); return r; }
+#endif
+RG_FN uint32_t fill_word(uint32_t s, uint32_t A)
 {
+    A &= 0x7FFFFFFFu;
+    return fill_up(s, A) | brev32(fill_up(brev32(s), brev32(A) >> 1));
+}
+
+template <class C, class Exec>
+RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s)
+{
+    /* Pass C needs no labels, only which voxels hang together with a selected component: start from the
+       representatives of the selected nodes and flood along the edge bit planes, 32 voxels per operation,
+       until nothing changes.  (The first version re-ran the union-find here; on tiles with one huge
+       component -- C3's background -- its hooks contend for a single root.) */
     int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
     const TileRec rc = P.rec[tile];
-    uint32_t *rootflag = s.openbits;                           /* bit r: tile-local root r is in the region */
 
     if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
-    ex.pfor(C::NW, [&](int i) { rootflag[i] = 0; });
+    const bool tma = ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0);
+    if (!tma) load_tile<C>(ex, P, s.img, x0, y0, z0, false);
+    ex.pfor(C::NW / 4, [&](int i) { st128(&s.M[4 * i], u32x4{0, 0, 0, 0}); });
     if (ex.tid() == 0) s.scal[SC_ANY] = 0;
     ex.sync();
     ex.pfor((int)rc.nnodes, [&](int i) {
         uint32_t g = rc.node_base + (uint32_t)i;
         if (find32(P.nparent, g) == 0u) {
             uint32_t r = P.nrep[g];
-            atomic_or(&rootflag[r >> 5], 1u << (r & 31));
+            atomic_or(&s.M[r >> 5], 1u << (r & 31));
             s.scal[SC_ANY] = 1;
         }
     });
-    ex.sync();
-    if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
-
-    if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, false);
     ex.tile_wait(&s.mbar);
     ex.sync();
-    build_edges<C, false>(ex, P, s, x0, y0, z0);
+    if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    build_edges<C, false>(ex, P, s.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
     ex.sync();
-    label_runs<C>(ex, s);
-
-    uint32_t *outw = s.seedbits;                               /* region bits per word */
-    ex.pfor(C::NW, [&](int w) {
-        int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
-        uint32_t exw = s.ex[w];
-        /* voxels with at least one edge; the others are singletons whose only way in is to be a root */
-        uint32_t he = exw | (exw << 1) | s.ey[w] | s.ez[w];
-        if (wx > 0) he |= s.ex[w - 1] >> 31;
-        if (y > 0) he |= s.ey[w - C::WX];
-        if (z > 0) he |= s.ez[w - C::WX * C::TY];
-        uint32_t out = rootflag[w] & ~he;
-        uint32_t S = ~(exw << 1), rem = S;
-        while (rem) {
-            int i = ffs1(rem) - 1; rem &= rem - 1;
-            int j = rem ? ffs1(rem) - 1 : 32;                  /* run = bits [i, j) */
-            uint32_t rm = (j == 32 ? 0xFFFFFFFFu : ((1u << j) - 1u)) & ~((1u << i) - 1u);
-            if (!(rm & he)) continue;
-            uint32_t r = find16(s.u.parent, (uint32_t)w * 32 + i);
-            if ((rootflag[r >> 5] >> (r & 31)) & 1u) out |= rm;
-        }
-        outw[w] = out;
-    });
-    ex.sync();
+    /* every word in parallel: take what the six neighbouring words offer through the edge planes, then close
+       the word's own x-runs; repeat until a sweep changes nothing (a region advances one word per sweep in
+       y and z, a whole run per sweep in x) */
+    bool changed;
+    do {
+        changed = false;
+        ex.pfor(C::NW, [&](int w) {
+            const int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+            const uint32_t m = s.M[w], exw = s.ex[w];
+            uint32_t in = m;
+            if (y > 0) in |= s.M[w - C::WX] & s.ey[w - C::WX];
+            if (y < C::TY - 1) in |= s.M[w + C::WX] & s.ey[w];
+            if (C::HZ) {
+                if (z > 0) in |= s.M[w - C::WX * C::TY] & s.ez[w - C::WX * C::TY];
+                if (z < C::TZ - 1) in |= s.M[w + C::WX * C::TY] & s.ez[w];
+            }
+            if (wx > 0) in |= (s.M[w - 1] & s.ex[w - 1]) >> 31;
+            if (wx < C::WX - 1) in |= ((s.M[w + 1] & 1u) << 31) & exw;
+            if (in) {
+                const uint32_t out = fill_word(in, exw);
+                if (out != m) { s.M[w] = out; changed = true; }
+            }
+        });
+    } while (ex.sync_or(changed));
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
         int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
         int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
         if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
-        uint32_t bits = (outw[(z * C::TY + y) * C::WX + (c >> 1)] >> ((c & 1) * 16)) & 0xFFFFu;
+        uint32_t bits = (s.M[(z * C::TY + y) * C::WX + (c >> 1)] >> ((c & 1) * 16)) & 0xFFFFu;
         u32x4 v = { expand4(bits & 15u), expand4((bits >> 4) & 15u), expand4((bits >> 8) & 15u), expand4(bits >> 12) };
         uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
         if (P.fast16) st128_stream(g, v);

@@ -170,7 +170,7 @@ template <class C>
 __global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
+    FloodSmem<C> &s = *reinterpret_cast<FloodSmem<C> *>(smem_raw);
     DevExec<RG_THREADS> ex; ex.tmap = &tmap;
     if (P.use_tma) ex.mbar_init(&s.mbar);
     pass_c_list<C>(ex, P, s);
@@ -415,7 +415,7 @@ static int set_attrs()
 {
     CK(cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<C>)));
     CK(cudaFuncSetAttribute(k_pass_a_full<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
-    CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FloodSmem<C>)));
     return RG_OK;
 }
 
@@ -480,10 +480,10 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
     if (c->last_P.debug_stop) { if (c->profile) cudaEventRecord(c->ev[4], st); return RG_OK; }   /* tuning runs time the fast pass only */
     if (c->last_is2d) {
         k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
-        k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
+        k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
     } else {
         k_flag_tiles<Cfg3D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
-        k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
+        k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
     }
     if (c->profile) cudaEventRecord(c->ev[4], st);
     CK(cudaGetLastError());

@@ -359,7 +359,7 @@ RG_FN void flag_tile(Exec &ex, const Params &P, uint32_t tile)
 }
 
 template <class C, class Exec>
-RG_FN void pass_c_list(Exec &ex, const Params &P, TileSmem<C> &s)
+RG_FN void pass_c_list(Exec &ex, const Params &P, FloodSmem<C> &s)
 {
     const uint32_t n = P.counters[CTR_NFLAGGED];
     for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {

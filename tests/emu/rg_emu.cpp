@@ -94,7 +94,7 @@ template <class C> static void emu_finish(EmuState &E)
 {
     HostExec ex; const Params &P = E.P;
     uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
-    TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(128, (sizeof(TileSmem<C>) + 127) / 128 * 128);
+    FloodSmem<C> *s = (FloodSmem<C> *)aligned_alloc(128, (sizeof(FloodSmem<C>) + 127) / 128 * 128);
     for (uint32_t t = 0; t < ntiles; t++) flag_tile<C>(ex, P, t);
     memset(s, 0x5A, sizeof *s);
     pass_c_list<C>(ex, P, *s);
