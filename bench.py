@@ -277,12 +277,12 @@ def main():
             img = torch.empty((n, n), dtype=torch.uint8, device=dev); ctx.synth(kind, img, n, seed)
             out = torch.empty_like(img); d_seeds = torch.from_numpy(seeds_np).to(dev)
             step = lambda: ctx.grow(img, d_seeds, T, out)
-            nvox, launches = n * n, 5
+            nvox, launches = n * n, 7          # keys, sort, fast label, full label, merge, flag/zero, pass C
         elif world == 1:
             img = torch.empty((n, n, n), dtype=torch.uint8, device=dev); ctx.synth(kind, img, n, seed)
             out = torch.empty_like(img); d_seeds = torch.from_numpy(seeds_np).to(dev)
             step = lambda: ctx.grow(img, d_seeds, T, out)
-            nvox, launches = n ** 3, 4 + (1 if len(seeds_np) > 1 else 0)
+            nvox, launches = n ** 3, 6 + (1 if len(seeds_np) > 1 else 0)
         else:
             g = rgb200.SlabGrower(lib, ctx.handle, n, n, n, rank, world, dev)
             plane = n * n
@@ -293,7 +293,7 @@ def main():
             step = lambda: g.grow(T)
             img, out = g.image, g.mask
             nvox = n ** 3
-            launches = 4 + 4 + 3 * world + 1          # label, 2x export, resolve init/union/apply, finish (upper bound)
+            launches = 6 + 4 + (2 * world + (world - 1) + 2) + 2   # label, 2x export (2 kernels each), resolve init/union/apply, flag + pass C (upper bound)
         for _ in range(warmup):
             step()
         barrier()
@@ -345,10 +345,17 @@ def main():
     n = args.n or WORKLOADS[wl][1]
     main_res = run(wl, n, args.steps, args.warmup, sample_clocks=True)
     kms = main_res["kernel_ms"]
-    dom = max(("pass_a", "pass_c"), key=lambda k: kms.get(k, 0.0))
+    # the two kernels that touch every voxel: the fast labelling pass reads 1 B/voxel, flag/zero-fill writes 1 B/voxel
+    dom = max(("pass_a_fast", "flag_tiles") if world == 1 else ("pass_a_fast",), key=lambda k: kms.get(k, 0.0))
     slab_vox = main_res["nvox"] / world                     # voxels one launch of the dominant kernel processes (per rank)
-    dom_bytes = 1.0 * slab_vox                              # pass A reads 1 B/voxel; pass C writes 1 B/voxel
+    dom_bytes = 1.0 * slab_vox
     achieved = dom_bytes / (kms[dom] * 1e-3) / 1e9 if kms.get(dom) else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic_r01.json")       # ncu --set full capture of this kernel on the default workload
+    if os.path.exists(tpath) and world == 1 and wl == "C4" and n == WORKLOADS["C4"][1]:
+        tj = json.load(open(tpath))
+        if tj.get("kernel") == "k_" + dom:
+            traffic = tj["dram_bytes_total"]
     path_gbs = ALGO_BYTES_PER_VOXEL * main_res["nvox"] / world / (main_res["ms_per_step"] * 1e-3) / 1e9
     line = {
         "metric": "Gvoxels/s (bit-exact mask)", "value": main_res["value"], "unit": "Gvoxels/s", "n_gpus": world,
@@ -363,7 +370,8 @@ def main():
         "gpu_launches": main_res["launches"] * args.steps,
         "clocks": main_res.get("clocks"),
         "roofline": {"bound": "hbm", "kernel": "k_" + dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": dom_bytes,
                      "algorithmic_bytes_per_voxel_kernel": 1.0, "kernel_ms": kms,
                      "path_bytes_per_voxel": ALGO_BYTES_PER_VOXEL, "path_achieved": path_gbs, "path_frac": path_gbs / peak},
     }

@@ -101,10 +101,11 @@ int64_t rg_noalloc_scratch_bytes(void);
 int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);
 
 /* Optional per-kernel timing with CUDA events on the launching stream (used by bench.py for the
- * roofline of the dominant kernel).  ms = {seed sort, pass A, pass B, pass C} of the last grow.
+ * roofline of the dominant kernel).  ms = {seed sort, fast labelling pass, full labelling pass, coarse
+ * merge, flag / zero-fill, pass C} of the last grow (multi-GPU: the interface exchange falls into `flag`).
  * Stands in for the gettimeofday()/print_time() pair around the grow call, raycast.cu:23-27,832-836. */
 int rg_ctx_profile(rg_ctx *ctx, int enable);
-int rg_ctx_profile_read(rg_ctx *ctx, float ms[4]);
+int rg_ctx_profile_read(rg_ctx *ctx, float ms[6]);
 
 /* replaces write_image()'s loop, region.c:575-577, on the device: image[i] *= (mask[i] == 0). */
 int rg_apply_mask_device(rg_ctx *ctx, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream);

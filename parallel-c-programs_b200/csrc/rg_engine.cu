@@ -277,7 +277,7 @@ struct rg_ctx {
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
     dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
-    bool profile; cudaEvent_t ev[5]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
+    bool profile; cudaEvent_t ev[7]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
 };
 
 /* cuTensorMapEncodeTiled through the runtime, so the library does not link against libcuda */
@@ -387,7 +387,7 @@ extern "C" void rg_ctx_destroy(rg_ctx *c)
     cudaSetDevice(c->device);
     cudaFree(c->ws); cudaFree(c->d_image); cudaFree(c->d_mask); cudaFree(c->d_seeds);
     cudaFreeHost(c->h_status);
-    if (c->ev_made) for (int i = 0; i < 5; i++) cudaEventDestroy(c->ev[i]);
+    if (c->ev_made) for (int i = 0; i < 7; i++) cudaEventDestroy(c->ev[i]);
     free(c);
 }
 
@@ -461,12 +461,13 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     const dim3 tile_grid = g3 ? dim3((unsigned)L.ntx, (unsigned)L.nty, (unsigned)L.ntz) : dim3(L.ntiles, 1, 1);
     c->last_grid = tile_grid;
     k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
-    if (!P.debug_stop) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
+    if (!P.debug_stop) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
+    if (c->profile) cudaEventRecord(c->ev[3], st);
     int64_t items = (int64_t)L.ntiles * 3;
     int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
     if (!P.debug_stop) k_merge<C><<<mb, 256, 0, st>>>(P);
-    if (c->profile) cudaEventRecord(c->ev[3], st);
+    if (c->profile) cudaEventRecord(c->ev[4], st);
     CK(cudaGetLastError());
     c->last_counters = P.counters; c->last_stream = st;
     c->last_P = P; c->last_is2d = (C::TZ == 1); c->last_ntiles = L.ntiles; c->have_last = true;
@@ -477,15 +478,17 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
 static int launch_finish(rg_ctx *c, cudaStream_t st)
 {
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
-    if (c->last_P.debug_stop) { if (c->profile) cudaEventRecord(c->ev[4], st); return RG_OK; }   /* tuning runs time the fast pass only */
+    if (c->last_P.debug_stop) { if (c->profile) { cudaEventRecord(c->ev[5], st); cudaEventRecord(c->ev[6], st); } return RG_OK; }   /* tuning runs time the fast pass only */
     if (c->last_is2d) {
         k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        if (c->profile) cudaEventRecord(c->ev[5], st);
         k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
     } else {
         k_flag_tiles<Cfg3D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        if (c->profile) cudaEventRecord(c->ev[5], st);
         k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
     }
-    if (c->profile) cudaEventRecord(c->ev[4], st);
+    if (c->profile) cudaEventRecord(c->ev[6], st);
     CK(cudaGetLastError());
     c->last_stream = st;
     return RG_OK;
@@ -611,17 +614,17 @@ extern "C" int rg_ctx_profile(rg_ctx *c, int enable)
 {
     if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
     CK(cudaSetDevice(c->device));
-    if (enable && !c->ev_made) { for (int i = 0; i < 5; i++) CK(cudaEventCreate(&c->ev[i])); c->ev_made = true; }
+    if (enable && !c->ev_made) { for (int i = 0; i < 7; i++) CK(cudaEventCreate(&c->ev[i])); c->ev_made = true; }
     c->profile = enable != 0;
     return RG_OK;
 }
 
-extern "C" int rg_ctx_profile_read(rg_ctx *c, float ms[4])
+extern "C" int rg_ctx_profile_read(rg_ctx *c, float ms[6])
 {
     if (!c || !ms || !c->ev_made) return fail(RG_ERR_ARG, "profiling was not enabled");
     CK(cudaSetDevice(c->device));
-    CK(cudaEventSynchronize(c->ev[4]));
-    for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms[i], c->ev[i], c->ev[i + 1]));
+    CK(cudaEventSynchronize(c->ev[6]));
+    for (int i = 0; i < 6; i++) CK(cudaEventElapsedTime(&ms[i], c->ev[i], c->ev[i + 1]));
     return RG_OK;
 }
 

@@ -235,9 +235,9 @@ class Context:
         _check(self.lib, self.lib.rg_ctx_profile(self.handle, 1 if enable else 0), "rg_ctx_profile")
 
     def profile_read(self):
-        ms = (ctypes.c_float * 4)()
+        ms = (ctypes.c_float * 6)()
         _check(self.lib, self.lib.rg_ctx_profile_read(self.handle, ms), "rg_ctx_profile_read")
-        return {"seed_sort": ms[0], "pass_a": ms[1], "pass_b": ms[2], "pass_c": ms[3]}
+        return {"seed_sort": ms[0], "pass_a_fast": ms[1], "pass_a_full": ms[2], "merge": ms[3], "flag_tiles": ms[4], "pass_c": ms[5]}
 
     def apply_mask(self, image, mask, stream=None):
         _check(self.lib, self.lib.rg_apply_mask_device(self.handle, image.data_ptr(), mask.data_ptr(), image.numel(),
