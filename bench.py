@@ -246,6 +246,8 @@ def main():
     dev = torch.device("cuda", local_rank)
     dist = None
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's banner / logs on stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     lib = rgb200.load_library()

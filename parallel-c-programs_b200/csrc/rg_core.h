@@ -523,7 +523,14 @@ RG_FN void merge_faces(Exec &ex, const Params &P)
             for (int f = 0; f < fb; f++) offb += rb.cnt[f];
             const uint16_t *ea = ta + here;
             const uint16_t *eb = P.ent + (size_t)nb * C::ENT_MAX + offb;
-            for (uint32_t i = lane; i < cnt; i += MERGE_LANES) unite32(P.nparent, ra.node_base + ea[i], rb.node_base + eb[i]);
+            /* faces inside a solid list the same pair of nodes hundreds of times: a lane skips a pair it has just united */
+            uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu;
+            for (uint32_t i = lane; i < cnt; i += MERGE_LANES) {
+                const uint32_t a = ra.node_base + ea[i], b = rb.node_base + eb[i];
+                if (a == pa && b == pb) continue;
+                unite32(P.nparent, a, b);
+                pa = a; pb = b;
+            }
         }
     });
 }

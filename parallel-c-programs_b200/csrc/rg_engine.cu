@@ -464,8 +464,8 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     if (c->profile) cudaEventRecord(c->ev[2], st);
     if (!P.debug_stop) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[3], st);
-    int64_t items = (int64_t)L.ntiles * 3;
-    int mb = (int)((items + 255) / 256); if (mb > 148 * 16) mb = 148 * 16;
+    int64_t items = (int64_t)L.ntiles * MERGE_LANES;                 /* one warp per tile */
+    int mb = (int)((items + 255) / 256); if (mb > 148 * 64) mb = 148 * 64;
     if (!P.debug_stop) k_merge<C><<<mb, 256, 0, st>>>(P);
     if (c->profile) cudaEventRecord(c->ev[4], st);
     CK(cudaGetLastError());
