@@ -188,7 +188,7 @@ def reference_c1_time():
             "gvoxels_per_s": 512 ** 3 / best / 1e9, "cores": 1, "kind": "reference"}
 
 
-def run_reference_arm(args, rank):
+def run_reference_arm(args, rank, emit):
     """--impl reference: the reference's CPU implementation of the path on the host cores.  The unmodified
     sources are fixed at 512^2 / 512^3 with compiled-in seeds, so for this workload the arm times the oracle
     port of region.c's distributed grow loop (pthreads) on a bounded sample; the unmodified serial grower on
@@ -216,7 +216,7 @@ def run_reference_arm(args, rank):
                              "sample": f"{wl} geometry at {ns}^{dims}, oracle_grow_par (region.c:493-533 rounds on {cores} threads)"},
             "e2e": {"value": val, "unit": "Gvoxels/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_unmodified": reference_c1_time()}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -230,12 +230,19 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="override the volume side (testing)")
     ap.add_argument("--no-extras", action="store_true", help="skip other_workloads / cpu_baseline / e2e (profiling runs)")
     args = ap.parse_args()
+    # stdout must carry exactly one JSON line: park the real stdout and send everything else (NCCL's banner,
+    # library chatter) to stderr
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    def emit(obj):
+        real_stdout.write(json.dumps(obj) + "\n"); real_stdout.flush()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.warmup < 3 and not args.no_extras:
         args.warmup = 3
     if args.impl == "reference":
-        run_reference_arm(args, rank)
+        run_reference_arm(args, rank, emit)
         return 0
 
     import torch
@@ -409,7 +416,7 @@ def main():
                                     "serial_1core_value": img.size / t_ser / 1e9,
                                     "reference_unmodified": reference_c1_time()}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -142,6 +142,12 @@ int rg_slab_resolve_init(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_roots,
 int rg_slab_resolve_union(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_upper_of_lower_rank, uint32_t off_lower_rank,
                           const uint32_t *d_lower_of_upper_rank, uint32_t off_upper_rank, uint32_t n, void *stream);
 int rg_slab_resolve_apply(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_own_roots, uint32_t n, uint32_t own_vertex_offset, void *stream);
+/* The three resolve steps for all interfaces of all ranks in one call (three launches): d_lists is the
+ * all-gathered buffer [world][2][stride] of interface lists, counts4 the all-gathered HOST array
+ * [world][4] = {entries towards lower, entries towards upper, node count, unused}.  Vertex offsets are
+ * the running sum of the node counts.  Equivalent to the init / union / apply calls above. */
+int rg_slab_resolve(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_lists, uint32_t stride, const int64_t *counts4,
+                    int rank, int world, void *stream);
 /* pass C on the slab labelled last */
 int rg_slab_finish(rg_ctx *ctx, void *stream);
 

@@ -107,6 +107,7 @@ struct Params {
     uint32_t node_cap;
     uint32_t *complex_list;      /* tiles the fast labelling pass handed to the full one */
     uint32_t *flag_list;         /* tiles that hold part of the region (pass C work list) */
+    int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tile then stores no zeros */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 

@@ -251,6 +251,23 @@ __global__ void __launch_bounds__(256) k_resolve_apply(const Params P, uint32_t 
     resolve_apply(ex, P, xpar, roots, n, off);
 }
 
+__global__ void __launch_bounds__(256) k_resolve_init_all(uint32_t *xpar, const uint32_t *lists, const ResolveArgs A)
+{
+    DevExec<256> ex;
+    if (blockIdx.x == 0 && threadIdx.x == 0) xpar[0] = 0;
+    resolve_init_all(ex, xpar, lists, A);
+}
+__global__ void __launch_bounds__(256) k_resolve_union_all(uint32_t *xpar, const uint32_t *lists, const ResolveArgs A)
+{
+    DevExec<256> ex;
+    resolve_union_all(ex, xpar, lists, A);
+}
+__global__ void __launch_bounds__(256) k_resolve_apply_all(const Params P, uint32_t *xpar, const uint32_t *lists, const ResolveArgs A)
+{
+    DevExec<256> ex;
+    resolve_apply_all(ex, P, xpar, lists, A);
+}
+
 /* ------------------------------------------------------------------ errors */
 static thread_local char g_err[512] = "";
 static int fail(int code, const char *what, cudaError_t e = cudaSuccess)
@@ -446,6 +463,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     uint64_t *keys = (uint64_t *)(ws + L.off_keys), *keys2 = (uint64_t *)(ws + L.off_keys2);
     P.seed_keys = keys;
 
+    P.mask_prezeroed = getenv("RG_NO_PREZERO") ? 0 : 1;          /* the labelling CTAs clear their own mask tile while their load is in flight */
     int kb = nseeds > 0 ? (nseeds + 255) / 256 : 1; if (kb > 1024) kb = 1024;
     if (c->profile) cudaEventRecord(c->ev[0], st);
     k_seed_keys<C><<<kb, 256, 0, st>>>(P, d_seeds, keys);
@@ -544,7 +562,7 @@ extern "C" int rg_slab_export(rg_ctx *c, int side, uint32_t *d_roots_out, uint32
     const Params &P = c->last_P;
     int nt = P.ntx * P.nty;
     k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_counts3 + side);
-    int b = (nt + 127) / 128;
+    int b = (nt * EXPORT_LANES + 127) / 128;
     k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots_out, d_counts3);
     CK(cudaGetLastError());
     return RG_OK;
@@ -578,6 +596,31 @@ extern "C" int rg_slab_resolve_apply(rg_ctx *c, uint32_t *d_xpar, const uint32_t
     CK(cudaSetDevice(c->device));
     if (!n) return RG_OK;
     k_resolve_apply<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(c->last_P, d_xpar, d_own_roots, n, own_vertex_offset);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_resolve(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_lists, uint32_t stride, const int64_t *counts4,
+                               int rank, int world, void *stream)
+{
+    if (!c || !c->have_last || !d_xpar || !d_lists || !counts4 || world < 2 || world > RESOLVE_MAX_RANKS || rank < 0 || rank >= world || !stride)
+        return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    ResolveArgs A; memset(&A, 0, sizeof A);
+    A.world = (uint32_t)world; A.rank = (uint32_t)rank; A.stride = stride;
+    uint64_t off = 1;
+    for (int r = 0; r < world; r++) {
+        A.cnt[r][0] = (uint32_t)counts4[4 * r]; A.cnt[r][1] = (uint32_t)counts4[4 * r + 1];
+        if (A.cnt[r][0] > stride || A.cnt[r][1] > stride) return fail(RG_ERR_ARG, "interface list longer than the stride");
+        A.off[r] = (uint32_t)off; off += (uint64_t)counts4[4 * r + 2];
+        if (off >= (1ull << 32)) return fail(RG_ERR_TOO_LARGE, "too many nodes across ranks for 32-bit vertex ids");
+    }
+    for (int r = 0; r + 1 < world; r++)
+        if (A.cnt[r][1] != A.cnt[r + 1][0]) return fail(RG_ERR_INTERNAL, "interface lists of neighbouring ranks differ in length");
+    cudaStream_t st = (cudaStream_t)stream;
+    k_resolve_init_all<<<blocks_for((uint32_t)world * 2u * stride), 256, 0, st>>>(d_xpar, d_lists, A);
+    k_resolve_union_all<<<blocks_for((uint32_t)(world - 1) * stride), 256, 0, st>>>(d_xpar, d_lists, A);
+    k_resolve_apply_all<<<blocks_for(2u * stride), 256, 0, st>>>(c->last_P, d_xpar, d_lists, A);
     CK(cudaGetLastError());
     return RG_OK;
 }

@@ -229,6 +229,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
 
     if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
+    if (P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);          /* fire-and-forget stores: they fill the load's latency */
     ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
     ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
     ex.pfor(HASH_N / 32, [&](int i) { s.seedtab[i] = 0; });
@@ -355,7 +356,7 @@ RG_FN void flag_tile(Exec &ex, const Params &P, uint32_t tile)
         if (ex.tid() == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
         return;
     }
-    zero_tile<C>(ex, P, x0, y0, z0);
+    if (!P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);
 }
 
 template <class C, class Exec>

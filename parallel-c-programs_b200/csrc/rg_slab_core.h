@@ -32,20 +32,23 @@ RG_FN void export_offsets(Exec &ex, const Params &P, int side, uint32_t *tile_of
     if (ex.tid() == 0) { tile_off[nt] = total; *count_out = total; }
 }
 
+enum { EXPORT_LANES = 32 };     /* one warp per boundary tile */
 template <class C, class Exec>
 RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *tile_off, uint32_t *out_roots)
 {
     const int nt = P.ntx * P.nty;
     const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
     const int f = side ? F_ZP : F_ZM;
-    ex.gpfor((int64_t)nt, [&](int64_t i) {
+    ex.gpfor((int64_t)nt * EXPORT_LANES, [&](int64_t it) {
+        const uint32_t lane = (uint32_t)(it % EXPORT_LANES);
+        const int64_t i = it / EXPORT_LANES;
         uint32_t tile = layer + (uint32_t)i;
         const TileRec &rc = P.rec[tile];
         uint32_t cnt = rc.cnt[f], off = 0;
         for (int k = 0; k < f; k++) off += rc.cnt[k];
         const uint16_t *e = P.ent + (size_t)tile * C::ENT_MAX + off;
         uint32_t *o = out_roots + tile_off[i];
-        for (uint32_t k = 0; k < cnt; k++) o[k] = find32(P.nparent, rc.node_base + e[k]);
+        for (uint32_t k = lane; k < cnt; k += EXPORT_LANES) o[k] = find32(P.nparent, rc.node_base + e[k]);
     });
 }
 
@@ -85,6 +88,44 @@ RG_FN void resolve_apply(Exec &ex, const Params &P, uint32_t *xpar, const uint32
     ex.gpfor((int64_t)n, [&](int64_t i) {
         uint32_t r = roots[i];
         if (r && find32(xpar, off + r) == 0u) unite32(P.nparent, r, 0u);
+    });
+}
+
+/* ---- all interfaces of all ranks in three sweeps (what rg_slab_resolve launches) ----
+   lists[(r * 2 + side) * stride + i]: rank r's list towards its lower (side 0) / upper (side 1) neighbour */
+enum { RESOLVE_MAX_RANKS = 64 };
+struct ResolveArgs {
+    uint32_t world, rank, stride, pad;
+    uint32_t cnt[RESOLVE_MAX_RANKS][2];
+    uint32_t off[RESOLVE_MAX_RANKS];
+};
+
+template <class Exec>
+RG_FN void resolve_init_all(Exec &ex, uint32_t *xpar, const uint32_t *lists, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)A.world * 2 * A.stride, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % A.stride), rs = (uint32_t)(it / A.stride), r = rs >> 1, side = rs & 1u;
+        if (i < A.cnt[r][side]) { uint32_t v = xvertex(lists[(size_t)rs * A.stride + i], A.off[r]); xpar[v] = v; }
+    });
+}
+template <class Exec>
+RG_FN void resolve_union_all(Exec &ex, uint32_t *xpar, const uint32_t *lists, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)(A.world - 1) * A.stride, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % A.stride), r = (uint32_t)(it / A.stride);
+        if (i < A.cnt[r][1])
+            unite32(xpar, xvertex(lists[(size_t)(r * 2 + 1) * A.stride + i], A.off[r]),
+                          xvertex(lists[(size_t)((r + 1) * 2) * A.stride + i], A.off[r + 1]));
+    });
+}
+template <class Exec>
+RG_FN void resolve_apply_all(Exec &ex, const Params &P, uint32_t *xpar, const uint32_t *lists, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)2 * A.stride, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % A.stride), side = (uint32_t)(it / A.stride);
+        if (i >= A.cnt[A.rank][side]) return;
+        const uint32_t r = lists[(size_t)(A.rank * 2 + side) * A.stride + i];
+        if (r && find32(xpar, A.off[A.rank] + r) == 0u) unite32(P.nparent, r, 0u);
     });
 }
 

@@ -48,6 +48,7 @@ class SlabGrower:
             self.all_counts = torch.zeros(self.world * 4, dtype=torch.int32, device=device)   # flat: gloo wants 1-D
         self.seeds_dev, self.nseeds = None, 0
         self.rounds = 0
+        self._timing = None
 
     # ---- helpers
     def _stream(self):
@@ -92,13 +93,34 @@ class SlabGrower:
             w.wait()
 
     # ---- the grow
+    def _mark(self, name):
+        """optional segment timing (RG_SLAB_TIMING=1): CUDA events on the current stream + host clock"""
+        if self._timing is None:
+            return
+        import time
+        ev = self.torch.cuda.Event(enable_timing=True); ev.record()
+        self._timing.append((name, ev, time.perf_counter()))
+
+    def timing_report(self):
+        if not self._timing:
+            return {}
+        self.torch.cuda.synchronize()
+        out = {}
+        for (n0, e0, t0), (n1, e1, t1) in zip(self._timing[:-1], self._timing[1:]):
+            out[n1] = {"gpu_ms": e0.elapsed_time(e1), "host_ms": (t1 - t0) * 1e3}
+        return out
+
     def grow(self, threshold):
         """enqueue label -> exchange -> resolve -> output; returns the slab's mask tensor"""
+        import os
+        self._timing = [] if (os.environ.get("RG_SLAB_TIMING") and self.use_cuda_stream) else None
+        self._mark("start")
         lib, st, plane = self.lib, self._stream(), self.nx * self.ny
         slab_ptr = self.buf.data_ptr() + plane
         self._ck(lib.rg_slab_label(self.ctx, slab_ptr, self.nx, self.ny, self.nzl, int(self.has_lower), int(self.has_upper),
                                    self.seeds_dev.data_ptr() if self.nseeds else None, self.nseeds, int(threshold),
                                    self.mask.data_ptr(), st), "rg_slab_label")
+        self._mark("label")
         if self.world > 1:
             torch, dist = self.torch, self.dist
             self.counts.zero_()
@@ -108,38 +130,29 @@ class SlabGrower:
                 self._ck(lib.rg_slab_export(self.ctx, 1, self.lists[1].data_ptr(), self.counts.data_ptr(), st), "rg_slab_export")
             if not (self.has_lower or self.has_upper):
                 raise RuntimeError("unreachable")
+            self._mark("export")
             dist.all_gather_into_tensor(self.all_counts, self.counts, group=self.group)
+            self._mark("gather_counts")
             cnt = self.all_counts.cpu().numpy().astype(np.int64).reshape(self.world, 4)          # the one host sync of the exchange
             for r in range(self.world - 1):
                 if cnt[r, 1] != cnt[r + 1, 0]:
                     raise RuntimeError(f"interface {r}/{r + 1}: list lengths differ ({cnt[r, 1]} vs {cnt[r + 1, 0]})")
             maxn = int(max(cnt[:, 0].max(), cnt[:, 1].max()))
+            self._mark("host_sync")
             if maxn > 0:
                 mine = self.lists[:, :maxn].contiguous()
                 flat = torch.empty(self.world * 2 * maxn, dtype=torch.int32, device=self.device)
                 dist.all_gather_into_tensor(flat, mine.view(-1), group=self.group)
                 gathered = flat.view(self.world, 2, maxn)
-                off = np.ones(self.world + 1, np.int64)
-                off[1:] = 1 + np.cumsum(cnt[:, 2])
-                xpar = torch.empty(int(off[-1]) + 1, dtype=torch.int32, device=self.device)
-                for r in range(self.world):
-                    for side in (0, 1):
-                        n = int(cnt[r, side])
-                        if n:
-                            self._ck(lib.rg_slab_resolve_init(self.ctx, xpar.data_ptr(), gathered[r, side].data_ptr(), n,
-                                                              int(off[r]), st), "rg_slab_resolve_init")
-                for r in range(self.world - 1):
-                    n = int(cnt[r, 1])
-                    if n:
-                        self._ck(lib.rg_slab_resolve_union(self.ctx, xpar.data_ptr(), gathered[r, 1].data_ptr(), int(off[r]),
-                                                           gathered[r + 1, 0].data_ptr(), int(off[r + 1]), n, st),
-                                 "rg_slab_resolve_union")
-                for side in (0, 1):
-                    n = int(cnt[self.rank, side])
-                    if n:
-                        self._ck(lib.rg_slab_resolve_apply(self.ctx, xpar.data_ptr(), gathered[self.rank, side].data_ptr(), n,
-                                                           int(off[self.rank]), st), "rg_slab_resolve_apply")
+                self._mark("gather_lists")
+                total_nodes = int(cnt[:, 2].sum())
+                xpar = torch.empty(total_nodes + 2, dtype=torch.int32, device=self.device)
+                cnt64 = np.ascontiguousarray(cnt, np.int64)
+                self._ck(lib.rg_slab_resolve(self.ctx, xpar.data_ptr(), flat.data_ptr(), maxn, cnt64.ctypes.data, self.rank, self.world, st),
+                         "rg_slab_resolve")
+                self._mark("resolve")
                 self._keepalive = (gathered, xpar, mine)
             self.rounds = 1
         self._ck(lib.rg_slab_finish(self.ctx, st), "rg_slab_finish")
+        self._mark("finish")
         return self.mask

@@ -62,6 +62,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.ntx = (int)((nx + C::TX - 1) / C::TX); P.nty = (int)((ny + C::TY - 1) / C::TY); P.ntz = (int)((nz + C::TZ - 1) / C::TZ);
     P.zlo_ext = zlo; P.zhi_ext = zhi;
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
+    P.mask_prezeroed = g_force_full ? 0 : 1;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
     size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
     size_t cap = 1 + ntiles * ((size_t)C::ENT_MAX + FAST_NODE_SLOTS) + (size_t)nseeds;
@@ -250,6 +251,19 @@ extern "C" int rg_slab_resolve_union(void *, uint32_t *xpar, const uint32_t *a, 
 extern "C" int rg_slab_resolve_apply(void *cv, uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off, void *)
 {
     EmuCtx *c = (EmuCtx *)cv; HostExec ex; resolve_apply(ex, c->E.P, xpar, roots, n, off); return 0;
+}
+extern "C" int rg_slab_resolve(void *cv, uint32_t *xpar, const uint32_t *lists, uint32_t stride, const int64_t *counts4, int rank, int world, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; HostExec ex;
+    ResolveArgs A; memset(&A, 0, sizeof A);
+    A.world = (uint32_t)world; A.rank = (uint32_t)rank; A.stride = stride;
+    uint32_t off = 1;
+    for (int r = 0; r < world; r++) { A.cnt[r][0] = (uint32_t)counts4[4 * r]; A.cnt[r][1] = (uint32_t)counts4[4 * r + 1]; A.off[r] = off; off += (uint32_t)counts4[4 * r + 2]; }
+    xpar[0] = 0;
+    resolve_init_all(ex, xpar, lists, A);
+    resolve_union_all(ex, xpar, lists, A);
+    resolve_apply_all(ex, c->E.P, xpar, lists, A);
+    return 0;
 }
 extern "C" int rg_slab_finish(void *cv, void *)
 {

@@ -10,7 +10,7 @@ import torch.multiprocessing as mp
 from conftest import ROOT, PKG
 
 SLAB_FNS = ["rg_ctx_create", "rg_ctx_destroy", "rg_last_error", "rg_slab_label", "rg_slab_interface_capacity",
-            "rg_slab_export", "rg_slab_resolve_init", "rg_slab_resolve_union", "rg_slab_resolve_apply", "rg_slab_finish"]
+            "rg_slab_export", "rg_slab_resolve", "rg_slab_resolve_init", "rg_slab_resolve_union", "rg_slab_resolve_apply", "rg_slab_finish"]
 
 
 def _worker(rank, world, port, img, seeds, T, cfg, out_q):
