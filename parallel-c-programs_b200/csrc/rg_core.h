@@ -354,26 +354,34 @@ RG_FN void label_runs(Exec &ex, TileSmem<C> &s)
         st128(&s.u.parent[v], q);
     });
     ex.sync();
+    /* three sweeps: links inside rows first, then between rows, then between planes -- each sweep starts from
+       trees the previous one has already flattened along one axis, which keeps the find paths short when a
+       tile holds one large component */
     ex.pfor(C::NW, [&](int w) {
-        int wx = w % C::WX;
-        uint32_t exw = s.ex[w];
-        if (wx > 0) {
-            uint32_t exl = s.ex[w - 1];
-            if (exl >> 31) unite16(s.u.parent, run_start(exl, w - 1, 31), (uint32_t)w * 32);
-        }
+        if (w % C::WX == 0) return;
+        uint32_t exl = s.ex[w - 1];
+        if (exl >> 31) unite16(s.u.parent, run_start(exl, w - 1, 31), (uint32_t)w * 32);
+    });
+    ex.sync();
+    ex.pfor(C::NW, [&](int w) {
         uint32_t m = s.ey[w];
-        if (m) {
-            int up = w + C::WX; uint32_t exu = s.ex[up];
-            uint32_t n = dedupe(m, exw, exu);
-            while (n) { int i = ffs1(n) - 1; n &= n - 1; unite16(s.u.parent, run_start(exw, w, i), run_start(exu, up, i)); }
-        }
-        m = s.ez[w];
-        if (m) {
+        if (!m) return;
+        uint32_t exw = s.ex[w];
+        int up = w + C::WX; uint32_t exu = s.ex[up];
+        uint32_t n = dedupe(m, exw, exu);
+        while (n) { int i = ffs1(n) - 1; n &= n - 1; unite16(s.u.parent, run_start(exw, w, i), run_start(exu, up, i)); }
+    });
+    if (C::HZ) {
+        ex.sync();
+        ex.pfor(C::NW, [&](int w) {
+            uint32_t m = s.ez[w];
+            if (!m) return;
+            uint32_t exw = s.ex[w];
             int up = w + C::WX * C::TY; uint32_t exu = s.ex[up];
             uint32_t n = dedupe(m, exw, exu);
             while (n) { int i = ffs1(n) - 1; n &= n - 1; unite16(s.u.parent, run_start(exw, w, i), run_start(exu, up, i)); }
-        }
-    });
+        });
+    }
     ex.sync();
 }
 
