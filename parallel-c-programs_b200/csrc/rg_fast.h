@@ -6,17 +6,18 @@
  * the inputs the reference generates (rand()%20 noise around a few solids, raycast.cu:114-144)
  * almost every component is a handful of voxels and only ~1 % of them reach a tile face.  So:
  *
- *   tile_pass_a_fast  one CTA per tile, ~56 KB smem (3 CTAs/SM): stage the tile, compute edge words
- *                     ONLY on the six face layers, then let one thread per cross-tile edge (and per
- *                     seed) walk its component directly on the staged bytes, at most WALK_MAX voxels.
- *                     The walk returns the component's smallest voxel index -- the same
- *                     representative the union-find of the full pass produces -- so nodes and face
- *                     lists are emitted exactly as in rg_core.h.  A tile in which any walk overflows
- *                     (a solid, a corridor ...) is appended to a work list and labelled by the full
- *                     pass instead; nothing is written for it here.
- *   flag_tiles        one small CTA per tile, no smem: decides whether any node of the tile ended up
- *                     in the region (root == node 0); if not, streams zeros over the tile's mask, else
- *                     appends the tile to the pass C work list.
+ *   tile_pass_a_fast  one CTA per tile, 68 KB smem (3 CTAs/SM): stage the tile with TMA and, while the load
+ *                     is in flight, clear the tile's part of the mask; compute edge words ONLY on the six
+ *                     face layers, then let one thread per cross-tile edge (and per seed) walk its
+ *                     component directly on the staged bytes, at most WALK_MAX voxels.  The walk returns
+ *                     the component's smallest voxel index -- the same representative the union-find of
+ *                     the full pass produces -- and a shared-memory hash table turns representatives
+ *                     into dense node ids, so nodes and face lists come out as in rg_core.h.  A tile in
+ *                     which any walk overflows (a solid's surface, a corridor ...) is appended to a work
+ *                     list and labelled by the full pass instead; nothing but zeros is written for it here.
+ *   flag_tile         one small CTA per tile, no smem: decides whether any node of the tile ended up in the
+ *                     region (root == node 0).  Uniform region tiles are filled with ones, the other region
+ *                     tiles are appended to the pass C work list; empty tiles were cleared by the fast pass.
  *
  * Same reference semantics as rg_core.h (region.c:493-533, raycast.cu:281-318); results are
  * identical whichever path a tile takes.
