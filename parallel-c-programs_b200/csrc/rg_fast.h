@@ -27,7 +27,10 @@
 
 namespace rg {
 
-enum { WALK_MAX = 16 };                       /* voxels a walk may visit before the tile is called complex */
+#ifndef RG_WALK_MAX
+#define RG_WALK_MAX 16
+#endif
+enum { WALK_MAX = RG_WALK_MAX };                     /* voxels a walk may visit before the tile is called complex */
 enum { FAST_ENT_MAX = 768 };                  /* cross-tile edges a non-uniform tile may have on the fast path */
 enum { HASH_BITS = 10, HASH_N = 1 << HASH_BITS, HASH_MAX_KEYS = 704 };
 static_assert((int)HASH_N == (int)FAST_NODE_SLOTS, "one node slot per hash slot");   /* representative -> dense node id */
@@ -40,31 +43,24 @@ struct alignas(128) FastSmem {
     uint16_t fprefix[C::FW_TOTAL + 2];
     uint16_t ent_root[FAST_ENT_MAX];              /* per edge: start voxel, later the hash slot of its component */
     uint16_t slow[FAST_ENT_MAX];                  /* edges whose start voxel has a similar neighbour inside the tile */
-    alignas(16) uint32_t tab[HASH_N];             /* open addressing: (representative + 1) << 16 | node id, 0 = empty */
+    alignas(16) uint32_t tab[HASH_N];             /* open addressing: representative + 1, 0 = empty */
+    uint16_t slotid[HASH_N];                      /* dense node id of each occupied slot (scan after the walks) */
     alignas(16) uint32_t seedtab[HASH_N / 32];    /* bit per slot: the component holds a seed */
     uint32_t scal[16];
     uint32_t scan_scratch[40];
     static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit");
 };
 
-/* find or insert representative `root`; the inserting thread hands out the next dense id.  Ids are read
-   back only after a barrier, so nobody waits on the short window in which a slot is claimed but unnumbered. */
+/* find or insert representative `root`; returns its slot.  Dense node ids are handed out afterwards by one
+   scan over the slots (a shared counter bumped by every inserting thread serialises the whole phase). */
 RG_FN uint32_t hash_slot(uint32_t *tab, uint32_t *scal, uint32_t root)
 {
-    const uint32_t key = (root + 1u) << 16;
+    const uint32_t key = root + 1u;
     uint32_t slot = (root * 2654435761u) >> (32 - HASH_BITS);
     for (int probe = 0; probe < HASH_N; probe++) {
         uint32_t cur = ldv32(&tab[slot]);
-        if (cur == 0u) {
-            cur = cas32(&tab[slot], 0u, key | 0xFFFFu);
-            if (cur == 0u) {
-                uint32_t id = atomic_add(&scal[SC_NNODES], 1u);
-                if (id >= (uint32_t)HASH_MAX_KEYS) { scal[SC_COMPLEX] = 1; id = 0; }
-                stv32(&tab[slot], key | id);
-                return slot;
-            }
-        }
-        if ((cur >> 16) == root + 1u) return slot;
+        if (cur == 0u) cur = cas32(&tab[slot], 0u, key);
+        if (cur == 0u || cur == key) return slot;
         slot = (slot + 1u) & (HASH_N - 1);
     }
     scal[SC_COMPLEX] = 1;
@@ -306,21 +302,25 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             const int e = s.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
-            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            const uint32_t nb0 = neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v);
+            if (P.debug_stop == 61) { s.ent_root[e] = (uint16_t)nb0; return; }
+            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, nb0, wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            if (P.debug_stop == 62) { s.ent_root[e] = (uint16_t)root; return; }
             s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, root);
         });
         ex.sync();
-        if (P.debug_stop == 7) return;
+        if (P.debug_stop == 7 || P.debug_stop == 61 || P.debug_stop == 62) return;
         if (s.scal[SC_COMPLEX]) { fast_give_up<C>(ex, P, tile); return; }
-        nnodes = s.scal[SC_NNODES];
-        /* node ids are final now: face lists and nodes go out in one sweep */
-        ex.pfor((int)etot, [&](int e) { ent[e] = (uint16_t)(s.tab[s.ent_root[e]] & 0xFFFFu); });
+        /* dense ids in slot order, then face lists and nodes go out in one sweep */
+        nnodes = ex.scan16(HASH_N, [&](int i) { return s.tab[i] ? 1u : 0u; }, s.slotid, s.scan_scratch);
+        if (nnodes > (uint32_t)HASH_MAX_KEYS) { fast_give_up<C>(ex, P, tile); return; }
+        ex.pfor((int)etot, [&](int e) { ent[e] = s.slotid[s.ent_root[e]]; });
         ex.pfor(HASH_N, [&](int slot) {
             const uint32_t cur = s.tab[slot];
             if (!cur) return;
-            const uint32_t g = base + (cur & 0xFFFFu);
+            const uint32_t g = base + s.slotid[slot];
             P.nparent[g] = ((s.seedtab[slot >> 5] >> (slot & 31)) & 1u) ? 0u : g;      /* seeded components start hooked to node 0 */
-            P.nrep[g] = (uint16_t)((cur >> 16) - 1u);
+            P.nrep[g] = (uint16_t)(cur - 1u);
         });
     }
     if (ex.tid() == 0) {
