@@ -449,9 +449,12 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
     ex.tile_wait(&s.mbar);
     ex.sync();
+    if (P.debug_stop == 10) return;
     build_edges<C, true>(ex, P, s.u.i.img, s.ex, s.ey, s.ez, s.fmask, x0, y0, z0);
     ex.sync();
+    if (P.debug_stop == 11) return;
     label_runs<C>(ex, s);
+    if (P.debug_stop == 12) return;
 
     /* positions of the face-list entries */
     uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
@@ -483,6 +486,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
         atomic_or(&s.openbits[r >> 5], 1u << (r & 31));
         s.ent_root[e] = (uint16_t)r;
     });
+    if (P.debug_stop == 13) return;
     /* ... or a seed */
     {
         int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];

@@ -480,7 +480,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     c->last_grid = tile_grid;
     k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
-    if (!P.debug_stop) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
+    if (!P.debug_stop || P.debug_stop >= 10 && P.debug_stop < 20) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[3], st);
     int64_t items = (int64_t)L.ntiles * MERGE_LANES;                 /* one warp per tile */
     int mb = (int)((items + 255) / 256); if (mb > 148 * 64) mb = 148 * 64;
