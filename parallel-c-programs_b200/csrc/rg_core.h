@@ -111,6 +111,12 @@ struct Params {
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
+#ifdef RG_PARENT32
+typedef uint32_t parent_t;     /* experiment: native 32-bit CAS, 1 CTA/SM */
+#else
+typedef uint16_t parent_t;
+#endif
+
 /* ---------------------------------------------------------------- shared-memory tile state */
 template <class C>
 struct alignas(128) TileSmem {
@@ -118,7 +124,7 @@ struct alignas(128) TileSmem {
         struct {
             uint8_t img[C::IMG_BYTES];             /* tile + 1-voxel halo, rows of RS bytes (see img_off) */
         } i;
-        uint16_t parent[C::NV];                    /* run union-find (image is dead by then) */
+        parent_t parent[C::NV];                    /* run union-find (image is dead by then) */
     } u;
     uint64_t mbar;                                 /* TMA completion barrier */
     uint32_t ex[C::NW], ey[C::NW], ez[C::NW];      /* bit i: voxel i similar to its +x/+y/+z neighbour (in-tile) */
@@ -222,6 +228,9 @@ RG_FN void unite32(uint32_t *par, uint32_t a, uint32_t b)
         a = old;
     }
 }
+
+RG_FN uint32_t find16(uint32_t *par, uint32_t x) { return find32(par, x); }
+RG_FN void unite16(uint32_t *par, uint32_t a, uint32_t b) { unite32(par, a, b); }
 
 template <class C>
 RG_FN void tile_origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz)
@@ -348,10 +357,14 @@ template <class C, class Exec>
 RG_FN void label_runs(Exec &ex, TileSmem<C> &s)
 {
     /* parent[v] = v, eight 16-bit entries per 16-byte store */
-    ex.pfor(C::NV / 8, [&](int it) {
+    if (sizeof(parent_t) == 2) ex.pfor(C::NV / 8, [&](int it) {
         uint32_t v = (uint32_t)it * 8;
         u32x4 q = { v | ((v + 1) << 16), (v + 2) | ((v + 3) << 16), (v + 4) | ((v + 5) << 16), (v + 6) | ((v + 7) << 16) };
         st128(&s.u.parent[v], q);
+    });
+    else ex.pfor(C::NV / 4, [&](int it) {
+        uint32_t v = (uint32_t)it * 4;
+        st128(&s.u.parent[v], u32x4{v, v + 1, v + 2, v + 3});
     });
     ex.sync();
     /* three sweeps: links inside rows first, then between rows, then between planes -- each sweep starts from

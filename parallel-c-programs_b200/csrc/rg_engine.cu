@@ -145,8 +145,13 @@ __global__ void __launch_bounds__(RG_FAST_THREADS, 3) k_pass_a_fast(const Params
 }
 
 /* pass A, full path: the tiles the fast path listed (persistent CTAs) */
+#ifdef RG_PARENT32
+#define RG_FULL_MINB 1
+#else
+#define RG_FULL_MINB 2
+#endif
 template <class C>
-__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_a_full(const Params P, const __grid_constant__ CUtensorMap tmap)
+__global__ void __launch_bounds__(RG_THREADS, RG_FULL_MINB) k_pass_a_full(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     TileSmem<C> &s = *reinterpret_cast<TileSmem<C> *>(smem_raw);
