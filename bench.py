@@ -317,6 +317,9 @@ def main():
         e1.record()
         barrier()
         ms = max_over_ranks(e0.elapsed_time(e1)) / steps
+        if dims == 3 and world > 1:
+            g.validate(T)                                  # optimistic exchanges: the device-side verdict (repeats the grow if refused)
+            res["optimistic_exchanges"] = g.optimistic_steps
         if sampler:
             res["clocks"] = sampler.stop()
         st = ctx.status()

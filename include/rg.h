@@ -148,6 +148,15 @@ int rg_slab_resolve_apply(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_own_r
  * the running sum of the node counts.  Equivalent to the init / union / apply calls above. */
 int rg_slab_resolve(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_lists, uint32_t stride, const int64_t *counts4,
                     int rank, int world, void *stream);
+/* Optimistic exchange (no host wait in mid-step).  The caller guesses capacities -- typically from the previous
+ * grow of the same volume: `cap` entries per interface list and `xpar_cap` vertices.  rg_slab_export_packed writes
+ * this rank's block {entries towards lower, entries towards upper, node id space, 0, lower list[cap], upper list[cap]}
+ * (4 + 2*cap words); the blocks of all ranks are all-gathered into d_packed_all; rg_slab_resolve_packed validates the
+ * counts ON THE DEVICE and resolves.  If a guess was too small nothing is written out of bounds: the status word gets
+ * bit 4 (rg_ctx_status then returns RG_ERR_INTERNAL) and the caller repeats the grow with rg_slab_export / rg_slab_resolve. */
+int rg_slab_export_packed(rg_ctx *ctx, uint32_t *d_packed, uint32_t cap, void *stream);
+int rg_slab_resolve_packed(rg_ctx *ctx, uint32_t *d_xpar, uint32_t xpar_cap, const uint32_t *d_packed_all, uint32_t cap,
+                           int rank, int world, void *stream);
 /* pass C on the slab labelled last */
 int rg_slab_finish(rg_ctx *ctx, void *stream);
 

@@ -233,11 +233,28 @@ __global__ void __launch_bounds__(1024) k_export_offsets(const Params P, int sid
     export_offsets<C>(ex, P, side, tile_off, count_out, scratch);
 }
 template <class C>
-__global__ void __launch_bounds__(128) k_export_entries(const Params P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t *counts3)
+__global__ void __launch_bounds__(128) k_export_entries(const Params P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t *counts3, uint32_t cap)
 {
     DevExec<128> ex;
     if (blockIdx.x == 0 && threadIdx.x == 0) counts3[2] = P.counters[CTR_NODES];
-    export_entries<C>(ex, P, side, tile_off, out_roots);
+    export_entries<C>(ex, P, side, tile_off, out_roots, cap);
+}
+__global__ void k_resolve_prepare(const Params P, const uint32_t *packed_all, uint32_t stride_words, uint32_t cap, uint32_t xpar_cap,
+                                  uint32_t rank, uint32_t world, ResolveArgs *A, uint32_t *xpar)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) { xpar[0] = 0; resolve_prepare(P, packed_all, stride_words, cap, xpar_cap, rank, world, A); }
+}
+__global__ void __launch_bounds__(256) k_resolve_init_packed(uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs *A)
+{
+    DevExec<256> ex; resolve_init_packed(ex, xpar, packed_all, cap, *A);
+}
+__global__ void __launch_bounds__(256) k_resolve_union_packed(uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs *A)
+{
+    DevExec<256> ex; resolve_union_packed(ex, xpar, packed_all, cap, *A);
+}
+__global__ void __launch_bounds__(256) k_resolve_apply_packed(const Params P, uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs *A)
+{
+    DevExec<256> ex; resolve_apply_packed(ex, P, xpar, packed_all, cap, *A);
 }
 __global__ void __launch_bounds__(256) k_resolve_init(uint32_t *xpar, const uint32_t *roots, uint32_t n, uint32_t off)
 {
@@ -297,6 +314,7 @@ struct rg_ctx {
     bool attr_set;
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
+    ResolveArgs *d_rargs;                      /* device copy of the exchange bookkeeping (optimistic exchange) */
     dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     bool profile; cudaEvent_t ev[7]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
@@ -336,7 +354,7 @@ static bool make_tmap(CUtensorMap *tm, const uint8_t *base, int64_t nx, int64_t 
 }
 
 struct Layout {
-    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, total;
+    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, off_rargs, total;
     uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
 };
 
@@ -370,6 +388,7 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
     L.off_if1 = o; o = align_up(o + ((size_t)ntx * nty + 1) * 4, 256);
     L.off_clist = o; o = align_up(o + (size_t)ntiles * 4, 256);
     L.off_flist = o; o = align_up(o + (size_t)ntiles * 4, 256);
+    L.off_rargs = o; o = align_up(o + sizeof(ResolveArgs), 256);
     L.total = o;
     return RG_OK;
 }
@@ -495,6 +514,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     c->last_counters = P.counters; c->last_stream = st;
     c->last_P = P; c->last_is2d = (C::TZ == 1); c->last_ntiles = L.ntiles; c->have_last = true;
     c->if_off[0] = (uint32_t *)(ws + L.off_if0); c->if_off[1] = (uint32_t *)(ws + L.off_if1);
+    c->d_rargs = (ResolveArgs *)(ws + L.off_rargs);
     return RG_OK;
 }
 
@@ -568,7 +588,7 @@ extern "C" int rg_slab_export(rg_ctx *c, int side, uint32_t *d_roots_out, uint32
     int nt = P.ntx * P.nty;
     k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_counts3 + side);
     int b = (nt * EXPORT_LANES + 127) / 128;
-    k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots_out, d_counts3);
+    k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots_out, d_counts3, 0xFFFFFFFFu);
     CK(cudaGetLastError());
     return RG_OK;
 }
@@ -626,6 +646,39 @@ extern "C" int rg_slab_resolve(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_li
     k_resolve_init_all<<<blocks_for((uint32_t)world * 2u * stride), 256, 0, st>>>(d_xpar, d_lists, A);
     k_resolve_union_all<<<blocks_for((uint32_t)(world - 1) * stride), 256, 0, st>>>(d_xpar, d_lists, A);
     k_resolve_apply_all<<<blocks_for(2u * stride), 256, 0, st>>>(c->last_P, d_xpar, d_lists, A);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_export_packed(rg_ctx *c, uint32_t *d_packed, uint32_t cap, void *stream)
+{
+    if (!c || !c->have_last || c->last_is2d || !d_packed || !cap) return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const Params &P = c->last_P;
+    CK(cudaMemsetAsync(d_packed, 0, 16, st));
+    int nt = P.ntx * P.nty, b = (nt * EXPORT_LANES + 127) / 128;
+    for (int side = 0; side < 2; side++) {
+        if (!(side ? P.zhi_ext : P.zlo_ext)) continue;
+        k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_packed + side);
+        k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_packed + 4 + (size_t)side * cap, d_packed, cap);
+    }
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_slab_resolve_packed(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar_cap, const uint32_t *d_packed_all, uint32_t cap,
+                                      int rank, int world, void *stream)
+{
+    if (!c || !c->have_last || !d_xpar || !d_packed_all || !cap || world < 2 || world > RESOLVE_MAX_RANKS || rank < 0 || rank >= world)
+        return fail(RG_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t stride = 4u + 2u * cap;
+    k_resolve_prepare<<<1, 32, 0, st>>>(c->last_P, d_packed_all, stride, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, c->d_rargs, d_xpar);
+    k_resolve_init_packed<<<blocks_for((uint32_t)world * 2u * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
+    k_resolve_union_packed<<<blocks_for((uint32_t)(world - 1) * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
+    k_resolve_apply_packed<<<blocks_for(2u * cap), 256, 0, st>>>(c->last_P, d_xpar, d_packed_all, cap, c->d_rargs);
     CK(cudaGetLastError());
     return RG_OK;
 }

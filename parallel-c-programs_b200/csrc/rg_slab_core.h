@@ -34,7 +34,7 @@ RG_FN void export_offsets(Exec &ex, const Params &P, int side, uint32_t *tile_of
 
 enum { EXPORT_LANES = 32 };     /* one warp per boundary tile */
 template <class C, class Exec>
-RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *tile_off, uint32_t *out_roots)
+RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t cap = 0xFFFFFFFFu)
 {
     const int nt = P.ntx * P.nty;
     const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
@@ -48,7 +48,9 @@ RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *t
         for (int k = 0; k < f; k++) off += rc.cnt[k];
         const uint16_t *e = P.ent + (size_t)tile * C::ENT_MAX + off;
         uint32_t *o = out_roots + tile_off[i];
-        for (uint32_t k = lane; k < cnt; k += EXPORT_LANES) o[k] = find32(P.nparent, rc.node_base + e[k]);
+        const uint32_t first = tile_off[i];
+        for (uint32_t k = lane; k < cnt; k += EXPORT_LANES)
+            if (first + k < cap) o[k] = find32(P.nparent, rc.node_base + e[k]);      /* a list longer than the buffer is reported, not written */
     });
 }
 
@@ -125,6 +127,63 @@ RG_FN void resolve_apply_all(Exec &ex, const Params &P, uint32_t *xpar, const ui
         const uint32_t i = (uint32_t)(it % A.stride), side = (uint32_t)(it / A.stride);
         if (i >= A.cnt[A.rank][side]) return;
         const uint32_t r = lists[(size_t)(A.rank * 2 + side) * A.stride + i];
+        if (r && find32(xpar, A.off[A.rank] + r) == 0u) unite32(P.nparent, r, 0u);
+    });
+}
+
+/* ---- optimistic exchange: capacities come from the previous step, so the host never waits in mid-step ----
+   packed[r] = { entries towards lower, entries towards upper, node id space, unused, lower list[cap], upper list[cap] }.
+   resolve_prepare turns the gathered counts into ResolveArgs on the device and refuses (status bit, empty
+   work) if a list outgrew `cap` or the vertex space outgrew `xpar_cap`. */
+enum { ST_EXCHANGE_OVERFLOW = 4u };
+RG_FN void resolve_prepare(const Params &P, const uint32_t *packed_all, uint32_t stride_words, uint32_t cap, uint32_t xpar_cap,
+                           uint32_t rank, uint32_t world, ResolveArgs *A)
+{
+    bool ok = true;
+    uint64_t off = 1;
+    A->world = world; A->rank = rank; A->stride = stride_words; A->pad = 0;
+    for (uint32_t r = 0; r < world; r++) {
+        const uint32_t *h = packed_all + (size_t)r * stride_words;
+        A->cnt[r][0] = h[0]; A->cnt[r][1] = h[1];
+        if (h[0] > cap || h[1] > cap) ok = false;
+        A->off[r] = (uint32_t)off; off += h[2];
+    }
+    for (uint32_t r = 0; r + 1 < world; r++) if (A->cnt[r][1] != A->cnt[r + 1][0]) ok = false;
+    if (off + 1 > (uint64_t)xpar_cap) ok = false;
+    if (!ok) {
+        for (uint32_t r = 0; r < world; r++) A->cnt[r][0] = A->cnt[r][1] = 0;
+        atomic_or(&P.counters[CTR_STATUS], ST_EXCHANGE_OVERFLOW);
+    }
+}
+/* list of (rank r, side) inside the packed buffer: header of 4 words, then the two lists */
+RG_FN const uint32_t *packed_list(const uint32_t *packed_all, const ResolveArgs &A, uint32_t cap, uint32_t r, uint32_t side)
+{
+    return packed_all + (size_t)r * A.stride + 4 + (size_t)side * cap;
+}
+template <class Exec>
+RG_FN void resolve_init_packed(Exec &ex, uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)A.world * 2 * cap, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % cap), rs = (uint32_t)(it / cap), r = rs >> 1, side = rs & 1u;
+        if (i < A.cnt[r][side]) { uint32_t v = xvertex(packed_list(packed_all, A, cap, r, side)[i], A.off[r]); xpar[v] = v; }
+    });
+}
+template <class Exec>
+RG_FN void resolve_union_packed(Exec &ex, uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)(A.world - 1) * cap, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % cap), r = (uint32_t)(it / cap);
+        if (i < A.cnt[r][1])
+            unite32(xpar, xvertex(packed_list(packed_all, A, cap, r, 1)[i], A.off[r]), xvertex(packed_list(packed_all, A, cap, r + 1, 0)[i], A.off[r + 1]));
+    });
+}
+template <class Exec>
+RG_FN void resolve_apply_packed(Exec &ex, const Params &P, uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs &A)
+{
+    ex.gpfor((int64_t)2 * cap, [&](int64_t it) {
+        const uint32_t i = (uint32_t)(it % cap), side = (uint32_t)(it / cap);
+        if (i >= A.cnt[A.rank][side]) return;
+        const uint32_t r = packed_list(packed_all, A, cap, A.rank, side)[i];
         if (r && find32(xpar, A.off[A.rank] + r) == 0u) unite32(P.nparent, r, 0u);
     });
 }

@@ -48,6 +48,8 @@ SIGNATURES = {
     "rg_slab_resolve_union": (_i32, [_vp, _vp, _vp, _u32, _vp, _u32, _u32, _vp]),
     "rg_slab_resolve_apply": (_i32, [_vp, _vp, _vp, _u32, _u32, _vp]),
     "rg_slab_resolve": (_i32, [_vp, _vp, _vp, _u32, _vp, _i32, _i32, _vp]),
+    "rg_slab_export_packed": (_i32, [_vp, _vp, _u32, _vp]),
+    "rg_slab_resolve_packed": (_i32, [_vp, _vp, _u32, _vp, _u32, _i32, _i32, _vp]),
     "rg_slab_finish": (_i32, [_vp, _vp]),
     "rg_synth_device": (_i32, [_i32, _vp, _i64, _u64, _vp]),
     "rg_synth_slab_device": (_i32, [_i32, _vp, _i64, _i64, _i64, _u64, _vp]),

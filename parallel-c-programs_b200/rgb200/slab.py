@@ -49,6 +49,9 @@ class SlabGrower:
         self.seeds_dev, self.nseeds = None, 0
         self.rounds = 0
         self._timing = None
+        self._cap = None            # capacities learnt from the last synchronous exchange (optimistic mode)
+        self._xpar_cap = 0
+        self.optimistic_steps = 0
 
     # ---- helpers
     def _stream(self):
@@ -110,8 +113,22 @@ class SlabGrower:
             out[n1] = {"gpu_ms": e0.elapsed_time(e1), "host_ms": (t1 - t0) * 1e3}
         return out
 
-    def grow(self, threshold):
-        """enqueue label -> exchange -> resolve -> output; returns the slab's mask tensor"""
+    def validate(self, threshold):
+        """after optimistic steps: synchronise and check the device-side verdict; if a guessed capacity was too small
+        the last grow is repeated with the synchronous exchange (which also refreshes the guesses)"""
+        st = (ctypes.c_uint32 * 4)()
+        rc = self.lib.rg_ctx_status(self.ctx, st)
+        if rc != 0 and (st[1] & 4):
+            self._cap = None
+            self.grow(threshold)
+            rc = self.lib.rg_ctx_status(self.ctx, st)
+        if rc != 0:
+            raise RuntimeError(f"slab grow failed: status=0x{st[1]:x}")
+        return self.mask
+
+    def grow(self, threshold, optimistic=True):
+        """enqueue label -> exchange -> resolve -> output; returns the slab's mask tensor.  With optimistic=True and
+        capacities known from an earlier grow, nothing waits on the host in mid-step (call validate() afterwards)."""
         import os
         self._timing = [] if (os.environ.get("RG_SLAB_TIMING") and self.use_cuda_stream) else None
         self._mark("start")
@@ -121,7 +138,18 @@ class SlabGrower:
                                    self.seeds_dev.data_ptr() if self.nseeds else None, self.nseeds, int(threshold),
                                    self.mask.data_ptr(), st), "rg_slab_label")
         self._mark("label")
-        if self.world > 1:
+        if self.world > 1 and optimistic and self._cap:
+            torch, dist = self.torch, self.dist
+            cap = self._cap
+            self._ck(lib.rg_slab_export_packed(self.ctx, self._packed.data_ptr(), cap, st), "rg_slab_export_packed")
+            self._mark("export")
+            dist.all_gather_into_tensor(self._allpacked, self._packed, group=self.group)
+            self._mark("gather_lists")
+            self._ck(lib.rg_slab_resolve_packed(self.ctx, self._xpar.data_ptr(), self._xpar_cap, self._allpacked.data_ptr(), cap,
+                                                self.rank, self.world, st), "rg_slab_resolve_packed")
+            self._mark("resolve")
+            self.optimistic_steps += 1
+        elif self.world > 1:
             torch, dist = self.torch, self.dist
             self.counts.zero_()
             if self.has_lower:
@@ -152,6 +180,12 @@ class SlabGrower:
                          "rg_slab_resolve")
                 self._mark("resolve")
                 self._keepalive = (gathered, xpar, mine)
+                # what the next, optimistic step may assume (25 % headroom)
+                self._cap = int(maxn * 1.25) + 1024
+                self._xpar_cap = int(total_nodes * 1.25) + 4096
+                self._packed = torch.zeros(4 + 2 * self._cap, dtype=torch.int32, device=self.device)
+                self._allpacked = torch.zeros(self.world * (4 + 2 * self._cap), dtype=torch.int32, device=self.device)
+                self._xpar = torch.empty(self._xpar_cap, dtype=torch.int32, device=self.device)
             self.rounds = 1
         self._ck(lib.rg_slab_finish(self.ctx, st), "rg_slab_finish")
         self._mark("finish")

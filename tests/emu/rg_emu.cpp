@@ -265,9 +265,40 @@ extern "C" int rg_slab_resolve(void *cv, uint32_t *xpar, const uint32_t *lists, 
     resolve_apply_all(ex, c->E.P, xpar, lists, A);
     return 0;
 }
+extern "C" int rg_slab_export_packed(void *cv, uint32_t *packed, uint32_t cap, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; HostExec ex;
+    const Params &P = c->E.P;
+    packed[0] = packed[1] = packed[2] = packed[3] = 0;
+    for (int side = 0; side < 2; side++) {
+        if (!(side ? P.zhi_ext : P.zlo_ext)) continue;
+        std::vector<uint32_t> off((size_t)P.ntx * P.nty + 1); uint32_t scratch[40];
+        DISPATCH(c->cfg, (export_offsets<C>(ex, P, side, off.data(), packed + side, scratch),
+                          export_entries<C>(ex, P, side, off.data(), packed + 4 + (size_t)side * cap, cap)));
+    }
+    packed[2] = c->E.counters[CTR_NODES];
+    return 0;
+}
+extern "C" int rg_slab_resolve_packed(void *cv, uint32_t *xpar, uint32_t xpar_cap, const uint32_t *packed_all, uint32_t cap, int rank, int world, void *)
+{
+    EmuCtx *c = (EmuCtx *)cv; HostExec ex;
+    ResolveArgs A; memset(&A, 0, sizeof A);
+    xpar[0] = 0;
+    resolve_prepare(c->E.P, packed_all, 4u + 2u * cap, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, &A);
+    resolve_init_packed(ex, xpar, packed_all, cap, A);
+    resolve_union_packed(ex, xpar, packed_all, cap, A);
+    resolve_apply_packed(ex, c->E.P, xpar, packed_all, cap, A);
+    return 0;
+}
+extern "C" int rg_ctx_status(void *cv, uint32_t *stats)
+{
+    EmuCtx *c = (EmuCtx *)cv;
+    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
+    return c->E.counters[CTR_STATUS] ? -4 : 0;
+}
 extern "C" int rg_slab_finish(void *cv, void *)
 {
     EmuCtx *c = (EmuCtx *)cv;
     DISPATCH(c->cfg, (emu_finish<C>(c->E)));
-    return c->E.counters[CTR_STATUS] ? -4 : 0;
+    return 0;     /* like the product: errors surface in rg_ctx_status */
 }

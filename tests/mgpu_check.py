@@ -38,7 +38,9 @@ def main():
         g.image.copy_(torch.from_numpy(img[g.z0:g.z1]).to(dev))
         g.exchange_image_halos()
         g.set_seeds(seeds)
-        m = g.grow(T)
+        m = g.grow(T)                      # synchronous exchange (learns capacities)
+        m = g.grow(T); m = g.validate(T)   # optimistic exchange
+        assert g.optimistic_steps == 1
         torch.cuda.synchronize()
         st = ctx.status()
         parts = [torch.empty((rgb200.slab_bounds(nz, r, world)[1] - rgb200.slab_bounds(nz, r, world)[0], ny, nx), dtype=torch.uint8, device=dev)

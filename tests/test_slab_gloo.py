@@ -10,7 +10,7 @@ import torch.multiprocessing as mp
 from conftest import ROOT, PKG
 
 SLAB_FNS = ["rg_ctx_create", "rg_ctx_destroy", "rg_last_error", "rg_slab_label", "rg_slab_interface_capacity",
-            "rg_slab_export", "rg_slab_resolve", "rg_slab_resolve_init", "rg_slab_resolve_union", "rg_slab_resolve_apply", "rg_slab_finish"]
+            "rg_slab_export", "rg_slab_resolve", "rg_slab_export_packed", "rg_slab_resolve_packed", "rg_ctx_status", "rg_slab_resolve_init", "rg_slab_resolve_union", "rg_slab_resolve_apply", "rg_slab_finish"]
 
 
 def _worker(rank, world, port, img, seeds, T, cfg, out_q):
@@ -29,7 +29,15 @@ def _worker(rank, world, port, img, seeds, T, cfg, out_q):
         g.image.copy_(torch.from_numpy(img[g.z0:g.z1]))
         g.exchange_image_halos()
         g.set_seeds(seeds)
-        m = g.grow(T)
+        m = g.grow(T)                                   # first grow: synchronous exchange, learns the capacities
+        first = m.numpy().copy()
+        m = g.grow(T)                                   # second grow: optimistic exchange (no host wait in mid-step)
+        m = g.validate(T)
+        assert g.optimistic_steps == 1 and (m.numpy() == first).all()
+        g._cap = 1; g._packed = torch.zeros(6, dtype=torch.int32); g._allpacked = torch.zeros(world * 6, dtype=torch.int32)
+        m = g.grow(T)                                   # a hopeless guess: the device refuses, validate() repeats the grow
+        m = g.validate(T)
+        assert (m.numpy() == first).all()
         out_q.put((rank, g.z0, g.z1, m.numpy().copy()))
         dist.barrier()
     except Exception as e:                                  # surface the failure instead of a queue timeout
