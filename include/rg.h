@@ -45,6 +45,16 @@ unsigned char *grow_region_gpu(unsigned char *data);
 unsigned char *grow_region_gpu_shared(unsigned char *data);
 unsigned char *grow_region_serial(unsigned char *data);
 
+/* replaces raycast_gpu()         5-cuda-region-growing/raycast.cu:436-470 (kernel :321-371)
+ *          raycast_gpu_texture() 5-cuda-region-growing/raycast.cu:472-531 (kernel :374-433; what main() runs, :842)
+ *          raycast_serial()      5-cuda-region-growing/raycast.cu:216-267 (same picture, computed on the GPU)
+ * and the OpenCL twin raycast_gpu() 6-opencl-region-growing/raycast.c:379-436 / raycast.cl:93-137.
+ * data, region = host 512^3 uint8 (region = the grower's mask).  Camera (1000,1000,1000) looking along
+ * (-1,-1,-1), 512 x 512 pixels, as the #defines of raycast.cu:14-17 say.  Returns a malloc'd 512 x 512 image
+ * the caller free()s (raycast.cu:853), NULL on failure. */
+unsigned char *raycast_gpu(unsigned char *data, unsigned char *region);
+unsigned char *raycast_gpu_texture(unsigned char *data, unsigned char *region);
+
 /* replaces the grow_region() + write_image() pair of 2-mpi-region-growing/region.c:493-533,572-580
  * for one whole image: seeds = the four corner seeds of add_seeds() (region.c:450-490) expressed
  * in global 0-based pixels (4,4),(w-6,4),(w-6,h-6),(4,h-6); threshold 2 (region.c:81).
@@ -109,6 +119,12 @@ int rg_ctx_profile_read(rg_ctx *ctx, float ms[6]);
 
 /* replaces write_image()'s loop, region.c:575-577, on the device: image[i] *= (mask[i] == 0). */
 int rg_apply_mask_device(rg_ctx *ctx, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream);
+
+/* The ray-caster on device-resident buffers, any cube side and image side (generalises raycast.cu:14-17):
+ * d_data, d_region = data_dim^3 bytes, d_image = image_dim^2 bytes, camera = the coordinate the reference
+ * puts on all three axes (1000).  Asynchronous on `stream`. */
+int rg_raycast_device(const uint8_t *d_data, const uint8_t *d_region, int data_dim, int image_dim, float camera,
+                      uint8_t *d_image, void *stream);
 
 const char *rg_last_error(void);
 

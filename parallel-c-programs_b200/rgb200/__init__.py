@@ -27,6 +27,8 @@ SIGNATURES = {
     "grow_region_gpu": (_vp, [_vp]),
     "grow_region_gpu_shared": (_vp, [_vp]),
     "grow_region_serial": (_vp, [_vp]),
+    "raycast_gpu": (_vp, [_vp, _vp]),
+    "raycast_gpu_texture": (_vp, [_vp, _vp]),
     "rg_grow_region_2d": (_i32, [_vp, _i32, _i32, _vp, _i32]),
     "rg_grow": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_ctx_create": (_i32, [_i32, _c.POINTER(_vp)]),
@@ -40,6 +42,7 @@ SIGNATURES = {
     "rg_ctx_profile": (_i32, [_vp, _i32]),
     "rg_ctx_profile_read": (_i32, [_vp, _vp]),
     "rg_apply_mask_device": (_i32, [_vp, _vp, _vp, _i64, _vp]),
+    "rg_raycast_device": (_i32, [_vp, _vp, _i32, _i32, _c.c_float, _vp, _vp]),
     "rg_last_error": (_c.c_char_p, []),
     "rg_slab_label": (_i32, [_vp, _vp, _i64, _i64, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp]),
     "rg_slab_interface_capacity": (_i64, [_i64, _i64]),
@@ -144,6 +147,45 @@ def grow_region_gpu(data):
 def grow_region_gpu_shared(data):
     """raycast.cu:759-822 (what the reference's main() calls, :833)"""
     return _grow_512("grow_region_gpu_shared", data)
+
+
+def _raycast_512(fn_name, data, region):
+    lib = load_library()
+    d = np.ascontiguousarray(data, np.uint8)
+    r = np.ascontiguousarray(region, np.uint8)
+    if d.size != 512 ** 3 or r.size != 512 ** 3:
+        raise ValueError("the reference-shaped entry points take 512^3 volumes (raycast.cu:11)")
+    ptr = getattr(lib, fn_name)(d.ctypes.data, r.ctypes.data)
+    if not ptr:
+        raise RGError(f"{fn_name} failed")
+    out = np.ctypeslib.as_array(ctypes.cast(ptr, ctypes.POINTER(ctypes.c_uint8)), (512, 512)).copy()
+    ctypes.CDLL(None).free(ctypes.c_void_p(ptr))
+    return out
+
+
+def raycast_gpu(data, region):
+    """raycast.cu:436-470"""
+    return _raycast_512("raycast_gpu", data, region)
+
+
+def raycast_gpu_texture(data, region):
+    """raycast.cu:472-531 (what the reference's main() calls, :842)"""
+    return _raycast_512("raycast_gpu_texture", data, region)
+
+
+def raycast_device(d_data, d_region, image_dim, camera=1000.0, stream=None, lib=None):
+    """rg_raycast_device on torch CUDA uint8 tensors (data_dim^3 each); returns the image tensor."""
+    import torch
+    lib = lib or load_library()
+    D = d_data.shape[0]
+    assert d_data.is_cuda and d_region.is_cuda and d_data.dtype == torch.uint8 and d_region.dtype == torch.uint8
+    assert tuple(d_data.shape) == (D, D, D) and tuple(d_region.shape) == (D, D, D)
+    assert d_data.is_contiguous() and d_region.is_contiguous()
+    img = torch.empty((image_dim, image_dim), dtype=torch.uint8, device=d_data.device)
+    with torch.cuda.device(d_data.device):
+        _check(lib, lib.rg_raycast_device(d_data.data_ptr(), d_region.data_ptr(), D, image_dim, float(camera),
+                                          img.data_ptr(), _stream_ptr(stream)), "rg_raycast_device")
+    return img
 
 
 def grow_region_2d(image, apply=False):

@@ -43,6 +43,7 @@ class Oracle:
         L.oracle_synth_c2.argtypes = [u8p, ctypes.c_int64, ctypes.c_uint64]
         L.oracle_seeds_c2.argtypes = [ctypes.c_int64, ctypes.c_void_p]
         L.oracle_synth_c3.argtypes = [u8p, ctypes.c_int64]
+        L.oracle_raycast.argtypes = [u8p, u8p, ctypes.c_int, ctypes.c_int, ctypes.c_float, u8p]
         L.oracle_c3_count.restype = ctypes.c_int64
         L.oracle_c3_count.argtypes = [ctypes.c_int64]
 
@@ -74,6 +75,13 @@ class Oracle:
                                      nthreads, mask.ctypes.data, ctypes.byref(rounds))
         assert n >= 0
         return mask, rounds.value
+
+    def raycast(self, data, region, image_dim, cam=1000.0):
+        data = np.ascontiguousarray(data, np.uint8); region = np.ascontiguousarray(region, np.uint8)
+        D = data.shape[0]
+        out = np.empty((image_dim, image_dim), np.uint8)
+        self.lib.oracle_raycast(data.ctypes.data, region.ctypes.data, D, image_dim, cam, out.ctypes.data)
+        return out
 
     def fnv(self, a):
         a = np.ascontiguousarray(a)

@@ -86,6 +86,16 @@ def main():
         "mask_values": sorted(int(v) for v in np.unique(msk)),
         "seed": [50, 300, 300], "threshold": 1,
     }
+    # the ray-caster that consumes the mask (raycast_serial, IMAGE_DIM = 64 as in 6-opencl-region-growing/raycast.c:16)
+    ref.ref_raycast_serial.restype = ctypes.c_void_p
+    ref.ref_raycast_serial.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    iptr = ref.ref_raycast_serial(dptr, mptr)
+    ray = np.ctypeslib.as_array(ctypes.cast(iptr, ctypes.POINTER(ctypes.c_uint8)), (64, 64)).copy()
+    gold["raycast64_sha256"] = hashlib.sha256(ray.tobytes()).hexdigest()
+    gold["raycast64_nonzero_px"] = int((ray > 0).sum())
+    arrays["ray64"] = ray
+    np.savez_compressed(os.path.join(HERE, "pics.npz"), **arrays)
+    ref.ref_free(iptr)
     ref.ref_free(mptr); ref.ref_free(dptr)
     json.dump(gold, open(os.path.join(HERE, "golden.json"), "w"), indent=1, sort_keys=True)
     print(json.dumps(gold, indent=1, sort_keys=True))

@@ -20,7 +20,7 @@ def declared_symbols():
     for h in ("rg.h", "bmp.h"):
         src = open(os.path.join(ROOT, "include", h)).read()
         src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-        names |= set(re.findall(r"\b((?:rg_|grow_region_|read_bmp|write_bmp)\w*)\s*\(", src))
+        names |= set(re.findall(r"\b((?:rg_|grow_region_|raycast_gpu|read_bmp|write_bmp)\w*)\s*\(", src))
     return names
 
 

@@ -83,3 +83,14 @@ def test_c3_count_formula(oracle):
         img, seeds, T = oracle.synth("c3", n)
         m = oracle.grow(img, seeds, T)
         assert int(m.sum()) == int((img == 200).sum()) == oracle.lib.oracle_c3_count(n)
+
+
+def test_raycast_restatement_equals_reference(oracle, golden):
+    """oracle_raycast (raycast.cu:183-267) at IMAGE_DIM 64 on the reference volume + mask == the unmodified
+    raycast_serial (golden ray64, produced by tests/golden/make_golden.py)"""
+    vol = oracle.create_data_ref()
+    mask = oracle.grow(vol, [golden["c1"]["seed"]], 1)
+    img = oracle.raycast(vol, mask, 64)
+    assert hashlib.sha256(img.tobytes()).hexdigest() == golden["raycast64_sha256"]
+    assert (img == golden["arrays"]["ray64"]).all()
+    assert int((img > 0).sum()) == golden["raycast64_nonzero_px"] > 500
