@@ -280,9 +280,16 @@ def main():
         seed = SEED_BASE + kind
         seeds_np = rgb200.synth_seeds(kind, n, seed)
         res = {"workload": desc, "n": n, "nseeds": int(len(seeds_np)), "threshold": T}
-        if dims == 2:
-            if world > 1:
-                raise SystemExit("C2 (2-D) is a single-GPU configuration")
+        if dims == 2 and world > 1:
+            g = rgb200.SlabGrower(lib, ctx.handle, n, n, 1, rank, world, dev)          # an image: row slabs
+            lo = g.z0 - (1 if g.has_lower else 0); hi = g.z1 + (1 if g.has_upper else 0)
+            ctx.synth(kind, g.buf[(lo - g.z0 + 1) * n:], n, seed, z_begin=lo, z_end=hi)  # own rows + the neighbours' boundary rows
+            g.set_seeds(seeds_np)
+            step = lambda: g.grow(T)
+            img, out = g.image, g.mask
+            nvox = n * n
+            launches = 7 + 4 + (2 * world + (world - 1) + 2) + 2
+        elif dims == 2:
             img = torch.empty((n, n), dtype=torch.uint8, device=dev); ctx.synth(kind, img, n, seed)
             out = torch.empty_like(img); d_seeds = torch.from_numpy(seeds_np).to(dev)
             step = lambda: ctx.grow(img, d_seeds, T, out)
@@ -317,7 +324,7 @@ def main():
         e1.record()
         barrier()
         ms = max_over_ranks(e0.elapsed_time(e1)) / steps
-        if dims == 3 and world > 1:
+        if world > 1:
             g.validate(T)                                  # optimistic exchanges: the device-side verdict (repeats the grow if refused)
             res["optimistic_exchanges"] = g.optimistic_steps
         if sampler:
@@ -375,7 +382,7 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"], "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": main_res["workload"], "n": n, "seeds": main_res["nseeds"], "threshold": main_res["threshold"],
-                   "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",
+                   "parallelism": (f"row slabs x{world}" if WORKLOADS[args.workload][2] == 2 else f"z-slabs x{world}") if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (no flush needed)" if main_res["nvox"] > 4e8 else "input+output ~2x L2; no flush",
                    "check": main_res["check"], "region_voxels": main_res["region_voxels"], "coarse_nodes": main_res["nodes"],
                    "tiles": {"total": -(-n // 64) * -(-n // 32) * -(-n // 16) if WORKLOADS[wl][2] == 3 else -(-n // 128) * -(-n // 126),
@@ -465,8 +472,8 @@ def run_e2e(torch, rgb200, lib, ctx, dist, dev, rank, world, wl, n, barrier, max
                 "d2h_bytes_per_step": int(nvox), "ms_per_step": sec * 1e3, "n": n_e2e, "region_voxels": cnt,
                 "api": "rg_grow (C ABI, pinned host image in, pinned host mask out)", "timer": "host wall clock around the synchronous call"}
     # N > 1: every rank moves its slab (+ halo planes) host->device, grows, and reads its mask slab back
-    g = rgb200.SlabGrower(lib, ctx.handle, n, n, n, rank, world, dev)
-    plane = n * n
+    g = rgb200.SlabGrower(lib, ctx.handle, n, n, 1 if dims == 2 else n, rank, world, dev)
+    plane = g.plane
     lo = g.z0 - (1 if g.has_lower else 0); hi = g.z1 + (1 if g.has_upper else 0)
     ctx.synth(kind, g.buf[(lo - g.z0 + 1) * plane:], n, seed, z_begin=lo, z_end=hi)
     h_buf = torch.empty(g.buf.shape, dtype=torch.uint8, pin_memory=True); h_buf.copy_(g.buf)
@@ -485,7 +492,7 @@ def run_e2e(torch, rgb200, lib, ctx, dist, dev, rank, world, wl, n, barrier, max
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1)) / steps
-    return {"value": n ** 3 / (ms * 1e-3) / 1e9, "unit": "Gvoxels/s", "h2d_bytes_per_step": int(h_buf.numel()),
+    return {"value": n ** dims / (ms * 1e-3) / 1e9, "unit": "Gvoxels/s", "h2d_bytes_per_step": int(h_buf.numel()),
             "d2h_bytes_per_step": int(h_out.numel()), "ms_per_step": ms, "n": n,
             "api": "rgb200.SlabGrower over rg_slab_* (C ABI), pinned host slab in, pinned host mask slab out; bytes are per rank"}
 

@@ -143,12 +143,16 @@ const char *rg_last_error(void);
 /* d_slab points at the slab's first own plane; if has_lower / has_upper the image planes just
  * below / above it (the neighbour's boundary planes, cf. distribute_image_halo) must be readable
  * at d_slab - nx*ny and d_slab + nz_local*nx*ny.  Seeds are slab-local (z - z0) and only those
- * inside the slab.  Enqueues seed sort + pass A + pass B. */
+ * inside the slab.  Enqueues seed sort + pass A + pass B.
+ * An IMAGE is cut into row slabs the same way (2-D inputs of region.c, whose MPI ranks each own a block of the picture,
+ * region.c:106-143): nz_local = 1, ny = the rank's own rows, seeds slab-local (y - y0), and the neighbours' boundary
+ * ROWS must be readable at d_slab - nx and d_slab + ny*nx.  A rank with a neighbour needs >= 2 planes (rows). */
 int rg_slab_label(rg_ctx *ctx, const uint8_t *d_slab, int64_t nx, int64_t ny, int64_t nz_local,
                   int has_lower, int has_upper, const int32_t *d_seeds_xyz, int nseeds, int threshold,
                   uint8_t *d_mask_slab, void *stream);
-/* worst-case number of entries of one interface list (size the export buffers with it) */
-int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny);
+/* worst-case number of entries of one interface list (size the export buffers with it); nz_local == 1 means
+ * row slabs of an image (the interface is a row), anything else z-slabs of a volume (the interface is a plane) */
+int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny, int64_t nz_local);
 /* side 0 = interface with the lower rank, 1 = with the upper rank.  d_roots_out receives, for every
  * cross-slab edge in canonical order, the local root node on this side; d_counts3[side] the
  * number of entries and d_counts3[2] the rank's node count. */
@@ -180,7 +184,8 @@ int rg_slab_finish(rg_ctx *ctx, void *stream);
 /* kind: 1 = exercise geometry with hash noise (C1h), 2 = C2 image (n x n), 3 = C3 serpentine,
  * 4 = C4 (exercise geometry + z-serpentine).  Cube / square of side n; seed = noise seed. */
 int rg_synth_device(int kind, uint8_t *d_out, int64_t n, uint64_t seed, void *stream);
-/* z-slab version: writes planes [z_begin, z_end) of the n^3 volume to d_out (slab-local). */
+/* slab version: writes planes [z_begin, z_end) of the n^3 volume to d_out (slab-local); for kind 2 (an image)
+ * the range is a ROW range and d_out points at row z_begin. */
 int rg_synth_slab_device(int kind, uint8_t *d_out, int64_t n, int64_t z_begin, int64_t z_end, uint64_t seed, void *stream);
 /* seed lists that go with the synthetic inputs; out = max_seeds*(x,y,z) host ints; returns count */
 int rg_synth_seeds(int kind, int64_t n, uint64_t seed, int32_t *out_xyz, int max_seeds);

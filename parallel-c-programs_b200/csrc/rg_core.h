@@ -91,7 +91,8 @@ struct Params {
     uint8_t *mask;
     int64_t nx, ny, nz;
     int32_t ntx, nty, ntz;
-    int32_t zlo_ext, zhi_ext;    /* slab has a neighbour slab below / above (multi-GPU) */
+    int32_t lo_ext, hi_ext;      /* slab has a neighbour slab below / above (multi-GPU) along the slab axis:
+                                    z for volumes (tiles with a z halo), y for images -- see ext_ylo() ... */
     int32_t tmode;               /* 0: T <= 0 (no edges)  1: 1..255  2: T >= 256 (all edges) */
     uint32_t t4;                 /* T replicated into 4 bytes */
     uint32_t thr;                /* scalar form: similar <=> |a-b| < thr  (0, T or 256) */
@@ -110,6 +111,12 @@ struct Params {
     int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tile then stores no zeros */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
+
+/* which axis a multi-GPU slab is cut along: z for volumes, y (rows) for images (tiles without a z halo) */
+template <class C> RG_HDFN int ext_zlo(const Params &P) { return C::HZ ? P.lo_ext : 0; }
+template <class C> RG_HDFN int ext_zhi(const Params &P) { return C::HZ ? P.hi_ext : 0; }
+template <class C> RG_HDFN int ext_ylo(const Params &P) { return C::HZ ? 0 : P.lo_ext; }
+template <class C> RG_HDFN int ext_yhi(const Params &P) { return C::HZ ? 0 : P.hi_ext; }
 
 #ifdef RG_PARENT32
 typedef uint32_t parent_t;     /* experiment: native 32-bit CAS, 1 CTA/SM */
@@ -253,7 +260,8 @@ RG_FN void load_tile(Exec &ex, const Params &P, uint8_t *img, int64_t x0, int64_
        in flight; the caller runs ex.tile_wait() + a barrier before reading.  The TMA path of the CUDA
        Exec (rg_engine.cu) produces the same bytes with one instruction per tile. */
     const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
-    const int64_t zmin = -(int64_t)P.zlo_ext, zmax = nz + P.zhi_ext;          /* readable plane range */
+    const int64_t zmin = -(int64_t)ext_zlo<C>(P), zmax = nz + ext_zhi<C>(P);    /* readable plane range */
+    const int64_t ymin = -(int64_t)ext_ylo<C>(P), ymax = ny + ext_yhi<C>(P);    /* readable row range (images cut into row slabs) */
     const bool fast = P.fast16 != 0;
     ex.pfor(C::PZ * C::PY * C::CXH, [&](int it) {
         int c = it % C::CXH, r = it / C::CXH;
@@ -263,13 +271,13 @@ RG_FN void load_tile(Exec &ex, const Params &P, uint8_t *img, int64_t x0, int64_
         bool want = !(yh && zh) && !(xh && (yh || zh)) && (halo || !(yh || zh || xh));
         if (!want) return;                                      /* never read: edge / corner columns, halo of pass C */
         int64_t gx = x0 - C::XO + 16 * c, gy = y0 + ly, gz = z0 + lz;
-        bool inside = gy >= 0 && gy < ny && gz >= zmin && gz < zmax && gx >= 0 && gx < nx;
-        if (xh) inside = inside && gz >= 0 && gz < nz;          /* x halo columns only matter for own rows */
+        bool inside = gy >= ymin && gy < ymax && gz >= zmin && gz < zmax && gx >= 0 && gx < nx;
+        if (xh) inside = inside && gz >= 0 && gz < nz && gy >= 0 && gy < ny;   /* x halo columns only matter for own rows */
         uint8_t *dst = &img[(pz * C::PY + py) * C::RS + 16 * c];
         if (fast) cp_async16(dst, P.image + (inside ? (gz * ny + gy) * nx + gx : 0), inside);
         else {
             uint32_t t[4] = {0, 0, 0, 0};
-            if (gy >= 0 && gy < ny && gz >= zmin && gz < zmax) {
+            if (gy >= ymin && gy < ymax && gz >= zmin && gz < zmax) {
                 const uint8_t *g = P.image + (gz * ny + gy) * nx;
                 for (int b = 0; b < 16; b++) if (gx + b >= 0 && gx + b < nx) t[b >> 2] |= (uint32_t)g[gx + b] << (8 * (b & 3));
             }
@@ -287,9 +295,9 @@ RG_FN void build_edges(Exec &ex, const Params &P, const uint8_t *img, uint32_t *
     const int tmode = P.tmode; const uint32_t t4 = P.t4;
     const int vy = (int)((ny - y0) < C::TY ? (ny - y0) : C::TY);
     const int vz = (int)((nz - z0) < C::TZ ? (nz - z0) : C::TZ);
-    const bool has_yp = y0 + C::TY < ny, has_ym = y0 > 0;
-    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && P.zhi_ext));
-    const bool has_zm = C::HZ && (z0 > 0 || P.zlo_ext);
+    const bool has_yp = (y0 + C::TY < ny) || (y0 + vy == ny && ext_yhi<C>(P)), has_ym = y0 > 0 || ext_ylo<C>(P);
+    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && ext_zhi<C>(P)));
+    const bool has_zm = C::HZ && (z0 > 0 || ext_zlo<C>(P));
     ex.pfor(C::NW, [&](int w) {
         int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
         int64_t gx0 = x0 + 32 * wx;
@@ -447,6 +455,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
     const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
+    const int vy = (int)((P.ny - y0) < C::TY ? (P.ny - y0) : C::TY);
 
     ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
     ex.pfor(C::NW, [&](int i) { s.openbits[i] = 0; s.seedbits[i] = 0; });
@@ -485,7 +494,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
             int b = ffs1(m) - 1; m &= m - 1;
             int x, y, z;
             if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
-            else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? C::TY - 1 : 0; }
+            else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? vy - 1 : 0; }
             else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
             s.ent_root[slot++] = (uint16_t)((z * C::TY + y) * C::TX + x);
         }

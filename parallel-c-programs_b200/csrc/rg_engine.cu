@@ -50,10 +50,10 @@ struct DevExec {
             const uint32_t b = smem_u32(bar);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     /* earlier generic-proxy accesses to this buffer */
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(b), "r"((uint32_t)C::IMG_BYTES) : "memory");
-            const int cx = (int)x0 - C::XO, cz = (int)z0 - C::HZ + P.zlo_ext;
+            const int cx = (int)x0 - C::XO, cz = (int)z0 - C::HZ + ext_zlo<C>(P), ylo = ext_ylo<C>(P);    /* the map starts at the lower halo plane / row */
 #pragma unroll
             for (int k = 0; k < C::TMA_NY; k++) {
-                const int cy = (int)y0 - 1 + k * C::BOXY;
+                const int cy = (int)y0 - 1 + ylo + k * C::BOXY;
                 asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                              :: "r"(smem_u32(img + k * C::BOXY * C::RS)), "l"((uint64_t)tmap), "r"(b), "r"(cx), "r"(cy), "r"(cz) : "memory");
             }
@@ -463,7 +463,7 @@ static int set_attrs()
 /* ------------------------------------------------------------------ the launch sequence */
 template <class C>
 static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
-                       int zlo_ext, int zhi_ext, const int32_t *d_seeds, int nseeds, int threshold,
+                       int lo_ext, int hi_ext, const int32_t *d_seeds, int nseeds, int threshold,
                        uint8_t *d_mask, cudaStream_t st)
 {
     char *ws = (char *)c->ws;
@@ -471,7 +471,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     memset(&P, 0, sizeof P);
     P.image = d_image; P.mask = d_mask; P.nx = nx; P.ny = ny; P.nz = nz;
     P.ntx = L.ntx; P.nty = L.nty; P.ntz = L.ntz;
-    P.zlo_ext = zlo_ext; P.zhi_ext = zhi_ext;
+    P.lo_ext = lo_ext; P.hi_ext = hi_ext;
     P.tmode = threshold <= 0 ? 0 : threshold >= 256 ? 2 : 1;
     P.t4 = (uint32_t)(threshold & 0xFF) * 0x01010101u;
     P.thr = threshold <= 0 ? 0u : threshold >= 256 ? 256u : (uint32_t)threshold;
@@ -479,7 +479,10 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.nseeds = nseeds;
     { static int dbg = -1; if (dbg < 0) { const char *e = getenv("RG_DEBUG_STOP"); dbg = e ? atoi(e) : 0; } P.debug_stop = dbg; }
     memset(&c->last_tmap, 0, sizeof c->last_tmap);
-    P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, d_image - (size_t)zlo_ext * nx * ny, nx, ny, nz + zlo_ext + zhi_ext)) ? 1 : 0;
+    /* the tensor map covers the neighbours' halo planes (volumes) or halo rows (images) as well */
+    const int64_t ey = ext_ylo<C>(P) + ext_yhi<C>(P), ez = ext_zlo<C>(P) + ext_zhi<C>(P);
+    const uint8_t *map_base = d_image - (size_t)ext_zlo<C>(P) * nx * ny - (size_t)ext_ylo<C>(P) * nx;
+    P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, map_base, nx, ny + ey, nz + ez)) ? 1 : 0;
     P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
     P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
     P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
@@ -537,7 +540,7 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
     return RG_OK;
 }
 
-static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
+static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int lo_ext, int hi_ext,
                             const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
 {
     if (!c || !d_image || !d_mask || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !d_seeds))
@@ -552,43 +555,56 @@ static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int6
     if (rc) return rc;
     rc = ensure_ws(c, L.total); if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    return nz == 1 ? launch_label<Cfg2D>(c, L, d_image, nx, ny, nz, 0, 0, d_seeds, nseeds, threshold, d_mask, st)
-                   : launch_label<Cfg3D>(c, L, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, st);
+    return nz == 1 ? launch_label<Cfg2D>(c, L, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, st)
+                   : launch_label<Cfg3D>(c, L, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, st);
 }
 
-static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int zlo_ext, int zhi_ext,
+static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int lo_ext, int hi_ext,
                             const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
 {
-    int rc = label_device_impl(c, d_image, nx, ny, nz, zlo_ext, zhi_ext, d_seeds, nseeds, threshold, d_mask, stream);
+    int rc = label_device_impl(c, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, stream);
     if (rc) return rc;
     return launch_finish(c, (cudaStream_t)stream);
 }
 
-/* ------------------------------------------------------------------ z-slab (multi-GPU) phases */
+/* ------------------------------------------------------------------ slab (multi-GPU) phases: z-slabs of a volume, row slabs of an image */
 extern "C" int rg_slab_label(rg_ctx *c, const uint8_t *d_slab, int64_t nx, int64_t ny, int64_t nz_local, int has_lower, int has_upper,
                              const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask_slab, void *stream)
 {
-    if (nz_local < 1) return fail(RG_ERR_ARG, "empty slab");
-    if (nz_local == 1 && (has_lower || has_upper)) return fail(RG_ERR_ARG, "one-plane slabs cannot have neighbours (use >= 2 planes per rank)");
+    if (nz_local < 1 || ny < 1) return fail(RG_ERR_ARG, "empty slab");
+    /* nz_local == 1 is an image cut into row slabs (ny = this rank's rows); a neighbour needs two rows / planes to face */
+    if ((has_lower || has_upper) && (nz_local == 1 ? ny : nz_local) < 2)
+        return fail(RG_ERR_ARG, "a slab with neighbours needs at least 2 planes (volume) or 2 rows (image) per rank");
     return label_device_impl(c, d_slab, nx, ny, nz_local, has_lower ? 1 : 0, has_upper ? 1 : 0, d_seeds_xyz, nseeds, threshold, d_mask_slab, stream);
 }
 
-extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny)
+extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny, int64_t nz_local)
 {
+    if (nz_local == 1) return (nx + Cfg2D::TX - 1) / Cfg2D::TX * (int64_t)Cfg2D::FYN;      /* one tile row's y faces */
     int64_t ntx = (nx + Cfg3D::TX - 1) / Cfg3D::TX, nty = (ny + Cfg3D::TY - 1) / Cfg3D::TY;
     return ntx * nty * (int64_t)Cfg3D::FZN;
 }
 
+/* one interface of the last labelled slab: entry count to *d_count, local roots to d_roots (at most cap of them) */
+static void export_side(rg_ctx *c, int side, uint32_t *d_count, uint32_t *d_roots, uint32_t *d_counts_base, uint32_t cap, cudaStream_t st)
+{
+    const Params &P = c->last_P;
+    if (c->last_is2d) {
+        const int b = (iface_tiles<Cfg2D>(P) * EXPORT_LANES + 127) / 128;
+        k_export_offsets<Cfg2D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_count);
+        k_export_entries<Cfg2D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots, d_counts_base, cap);
+    } else {
+        const int b = (iface_tiles<Cfg3D>(P) * EXPORT_LANES + 127) / 128;
+        k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_count);
+        k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots, d_counts_base, cap);
+    }
+}
+
 extern "C" int rg_slab_export(rg_ctx *c, int side, uint32_t *d_roots_out, uint32_t *d_counts3, void *stream)
 {
-    if (!c || !c->have_last || c->last_is2d || !d_roots_out || !d_counts3 || side < 0 || side > 1) return fail(RG_ERR_ARG, "bad argument");
+    if (!c || !c->have_last || !d_roots_out || !d_counts3 || side < 0 || side > 1) return fail(RG_ERR_ARG, "bad argument");
     CK(cudaSetDevice(c->device));
-    cudaStream_t st = (cudaStream_t)stream;
-    const Params &P = c->last_P;
-    int nt = P.ntx * P.nty;
-    k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_counts3 + side);
-    int b = (nt * EXPORT_LANES + 127) / 128;
-    k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_roots_out, d_counts3, 0xFFFFFFFFu);
+    export_side(c, side, d_counts3 + side, d_roots_out, d_counts3, 0xFFFFFFFFu, (cudaStream_t)stream);
     CK(cudaGetLastError());
     return RG_OK;
 }
@@ -652,16 +668,14 @@ extern "C" int rg_slab_resolve(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_li
 
 extern "C" int rg_slab_export_packed(rg_ctx *c, uint32_t *d_packed, uint32_t cap, void *stream)
 {
-    if (!c || !c->have_last || c->last_is2d || !d_packed || !cap) return fail(RG_ERR_ARG, "bad argument");
+    if (!c || !c->have_last || !d_packed || !cap) return fail(RG_ERR_ARG, "bad argument");
     CK(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
     const Params &P = c->last_P;
     CK(cudaMemsetAsync(d_packed, 0, 16, st));
-    int nt = P.ntx * P.nty, b = (nt * EXPORT_LANES + 127) / 128;
     for (int side = 0; side < 2; side++) {
-        if (!(side ? P.zhi_ext : P.zlo_ext)) continue;
-        k_export_offsets<Cfg3D><<<1, 1024, 0, st>>>(P, side, c->if_off[side], d_packed + side);
-        k_export_entries<Cfg3D><<<b, 128, 0, st>>>(P, side, c->if_off[side], d_packed + 4 + (size_t)side * cap, d_packed, cap);
+        if (!(side ? P.hi_ext : P.lo_ext)) continue;
+        export_side(c, side, d_packed + side, d_packed + 4 + (size_t)side * cap, d_packed, cap, st);
     }
     CK(cudaGetLastError());
     return RG_OK;

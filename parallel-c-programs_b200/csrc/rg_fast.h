@@ -138,11 +138,11 @@ RG_FN bool walk_component(const uint8_t *img, int vx, int vy, int vz, uint32_t t
 
 /* voxel (tile-local linear index) on this side of cross-tile edge `b` of face word (f, idx) */
 template <class C>
-RG_FN uint32_t face_voxel(int f, int idx, int b, int vz)
+RG_FN uint32_t face_voxel(int f, int idx, int b, int vy, int vz)
 {
     int x, y, z;
     if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
-    else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? C::TY - 1 : 0; }
+    else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? vy - 1 : 0; }
     else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
     return (uint32_t)((z * C::TY + y) * C::TX + x);
 }
@@ -156,9 +156,9 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint3
     const int tmode = P.tmode; const uint32_t t4 = P.t4;
     const int vy = (int)((ny - y0) < C::TY ? (ny - y0) : C::TY);
     const int vz = (int)((nz - z0) < C::TZ ? (nz - z0) : C::TZ);
-    const bool has_yp = y0 + C::TY < ny, has_ym = y0 > 0;
-    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && P.zhi_ext));
-    const bool has_zm = C::HZ && (z0 > 0 || P.zlo_ext);
+    const bool has_yp = (y0 + C::TY < ny) || (y0 + vy == ny && ext_yhi<C>(P)), has_ym = y0 > 0 || ext_ylo<C>(P);
+    const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && ext_zhi<C>(P)));
+    const bool has_zm = C::HZ && (z0 > 0 || ext_zlo<C>(P));
     const bool has_xp = x0 + C::TX < nx, has_xm = x0 > 0;
     /* y faces: item = (side, z, wx); z faces: item = (side, y, wx) */
     ex.pfor(2 * C::FYW + 2 * C::FZW, [&](int it) {
@@ -170,7 +170,7 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint3
         int y, z, step, f;
         if (!zface) {
             if (side ? !has_yp : !has_ym) return;
-            z = o; y = side ? C::TY - 1 : 0; step = side ? C::RS : -C::RS; f = side ? F_YP : F_YM;
+            z = o; y = side ? vy - 1 : 0; step = side ? C::RS : -C::RS; f = side ? F_YP : F_YM;
             if (z >= vz) return;
         } else {
             if (side ? !has_zp : !has_zm) return;
@@ -276,7 +276,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             int f = 0; while (fw >= C::fw_off(f + 1)) f++;
             const int idx = fw - C::fw_off(f);
             uint32_t slot = s.fprefix[fw];
-            while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vz); }
+            while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vy, vz); }
         });
         ex.sync();
         /* ... then one thread per edge.  Most start voxels have no similar neighbour inside the tile and are their

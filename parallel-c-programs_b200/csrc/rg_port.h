@@ -14,10 +14,12 @@
 #if defined(__CUDACC__)
 #define RG_FN __device__ __forceinline__
 #define RG_MFN __device__ __forceinline__
+#define RG_HDFN __host__ __device__ __forceinline__
 #define RG_DEVICE_BUILD 1
 #else
 #define RG_FN static inline
 #define RG_MFN inline
+#define RG_HDFN static inline
 #define RG_DEVICE_BUILD 0
 #include <string.h>
 #endif

@@ -1,5 +1,5 @@
 /*
- * rg_slab_core.h -- kernel bodies of the multi-GPU (z-slab) path.
+ * rg_slab_core.h -- kernel bodies of the multi-GPU slab path (z-slabs of a volume, row slabs of an image).
  *
  * Replaces the distributed half of 2-mpi-region-growing/region.c: exchange() (:250-353),
  * add_halo_to_stack() (:355-387) and finished() (:435-440).  The reference swaps mask borders
@@ -20,14 +20,25 @@
 
 namespace rg {
 
-/* side 0: ZM faces of the bottom tile layer; side 1: ZP faces of the top tile layer.
- * tile_off[0..ntx*nty] = exclusive prefix of the per-tile entry counts (scratch, written here). */
+/* The interface of a slab: volumes are cut along z (the tile layers tz = 0 / ntz-1 with their ZM / ZP faces),
+ * images along y (the tile rows ty = 0 / nty-1 with their YM / YP faces; nz = ntz = 1).  Tiles of a layer / row
+ * are consecutive in tile order either way. */
+template <class C> RG_HDFN int iface_tiles(const Params &P) { return C::HZ ? P.ntx * P.nty : P.ntx; }
+template <class C> RG_HDFN uint32_t iface_first_tile(const Params &P, int side)
+{
+    if (!side) return 0u;
+    return C::HZ ? (uint32_t)(P.ntz - 1) * (uint32_t)(P.ntx * P.nty) : (uint32_t)(P.nty - 1) * (uint32_t)P.ntx;
+}
+template <class C> RG_HDFN int iface_face(int side) { return C::HZ ? (side ? F_ZP : F_ZM) : (side ? F_YP : F_YM); }
+
+/* side 0: lower faces of the bottom tile layer; side 1: upper faces of the top tile layer.
+ * tile_off[0..iface_tiles] = exclusive prefix of the per-tile entry counts (scratch, written here). */
 template <class C, class Exec>
 RG_FN void export_offsets(Exec &ex, const Params &P, int side, uint32_t *tile_off, uint32_t *count_out, uint32_t *scratch)
 {
-    const int nt = P.ntx * P.nty;
-    const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
-    const int f = side ? F_ZP : F_ZM;
+    const int nt = iface_tiles<C>(P);
+    const uint32_t layer = iface_first_tile<C>(P, side);
+    const int f = iface_face<C>(side);
     uint32_t total = ex.scan32(nt, [&](int i) { return (uint32_t)P.rec[layer + (uint32_t)i].cnt[f]; }, tile_off, scratch);
     if (ex.tid() == 0) { tile_off[nt] = total; *count_out = total; }
 }
@@ -36,9 +47,9 @@ enum { EXPORT_LANES = 32 };     /* one warp per boundary tile */
 template <class C, class Exec>
 RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *tile_off, uint32_t *out_roots, uint32_t cap = 0xFFFFFFFFu)
 {
-    const int nt = P.ntx * P.nty;
-    const uint32_t layer = side ? (uint32_t)(P.ntz - 1) * (uint32_t)nt : 0u;
-    const int f = side ? F_ZP : F_ZM;
+    const int nt = iface_tiles<C>(P);
+    const uint32_t layer = iface_first_tile<C>(P, side);
+    const int f = iface_face<C>(side);
     ex.gpfor((int64_t)nt * EXPORT_LANES, [&](int64_t it) {
         const uint32_t lane = (uint32_t)(it % EXPORT_LANES);
         const int64_t i = it / EXPORT_LANES;
@@ -59,7 +70,7 @@ RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *t
 template <class C, class Exec>
 RG_FN void export_interface(Exec &ex, const Params &P, int side, uint32_t *out_roots, uint32_t *count_out)
 {
-    const int nt = P.ntx * P.nty;
+    const int nt = iface_tiles<C>(P);
     uint32_t *tile_off = new uint32_t[(size_t)nt + 1];
     uint32_t scratch[40];
     export_offsets<C>(ex, P, side, tile_off, count_out, scratch);

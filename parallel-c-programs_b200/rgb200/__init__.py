@@ -45,7 +45,7 @@ SIGNATURES = {
     "rg_raycast_device": (_i32, [_vp, _vp, _i32, _i32, _c.c_float, _vp, _vp]),
     "rg_last_error": (_c.c_char_p, []),
     "rg_slab_label": (_i32, [_vp, _vp, _i64, _i64, _i64, _i32, _i32, _vp, _i32, _i32, _vp, _vp]),
-    "rg_slab_interface_capacity": (_i64, [_i64, _i64]),
+    "rg_slab_interface_capacity": (_i64, [_i64, _i64, _i64]),
     "rg_slab_export": (_i32, [_vp, _i32, _vp, _vp, _vp]),
     "rg_slab_resolve_init": (_i32, [_vp, _vp, _vp, _u32, _u32, _vp]),
     "rg_slab_resolve_union": (_i32, [_vp, _vp, _vp, _u32, _vp, _u32, _u32, _vp]),

@@ -1,4 +1,5 @@
-"""Multi-rank z-slab driver: one process per GPU, torch.distributed for the plumbing.
+"""Multi-rank slab driver: one process per GPU, torch.distributed for the plumbing.  A volume is cut into z-slabs,
+an image (nz == 1) into row slabs -- either way each rank owns a contiguous range of the slowest axis.
 
 Mirrors the distributed half of the reference's 2-D MPI program (2-mpi-region-growing/region.c):
   distribute_image_halo (:145-246)  -> exchange_image_halos(): one static boundary-plane swap
@@ -29,19 +30,25 @@ class SlabGrower:
         self.rank, self.world, self.group = int(rank), int(world), group
         self.device = device
         self.use_cuda_stream = use_cuda_stream
-        self.z0, self.z1 = slab_bounds(self.nz, self.rank, self.world)
+        # the slab axis: z for a volume, y (rows) for an image; z0 / z1 / nzl are positions along THAT axis and
+        # "plane" below is one unit of it (a plane of nx*ny voxels, or a row of nx pixels)
+        self.rows = self.nz == 1
+        self.axis = 1 if self.rows else 2
+        self.plane = self.nx if self.rows else self.nx * self.ny
+        self.z0, self.z1 = slab_bounds(self.ny if self.rows else self.nz, self.rank, self.world)
         self.nzl = self.z1 - self.z0
         if self.world > 1 and self.nzl < 2:
-            raise ValueError("each rank needs at least 2 planes")
+            raise ValueError("each rank needs at least 2 planes (rows)")
         self.has_lower = self.rank > 0
         self.has_upper = self.rank < self.world - 1
-        plane = self.nx * self.ny
+        plane = self.plane
+        shape = (self.nzl, self.nx) if self.rows else (self.nzl, self.ny, self.nx)
         # slab with one halo plane on each side (present even when unused: keeps offsets simple)
         self.buf = torch.zeros((self.nzl + 2) * plane, dtype=torch.uint8, device=device)
-        self.image = self.buf[plane:(self.nzl + 1) * plane].view(self.nzl, self.ny, self.nx)
-        self.mask = torch.empty((self.nzl, self.ny, self.nx), dtype=torch.uint8, device=device)
+        self.image = self.buf[plane:(self.nzl + 1) * plane].view(*shape)
+        self.mask = torch.empty(shape, dtype=torch.uint8, device=device)
         if self.world > 1:
-            cap = int(lib.rg_slab_interface_capacity(self.nx, self.ny))
+            cap = int(lib.rg_slab_interface_capacity(self.nx, self.ny, 1 if self.rows else self.nzl))
             self.cap = cap
             self.lists = torch.zeros((2, cap), dtype=torch.int32, device=device)
             self.counts = torch.zeros(4, dtype=torch.int32, device=device)
@@ -65,12 +72,13 @@ class SlabGrower:
             raise RuntimeError(f"{what} failed with {rc}: {msg.decode() if msg else ''}")
 
     def set_seeds(self, seeds_global):
-        """keep the seeds that fall into this slab, in slab-local z (add_seeds, region.c:450-490:
+        """keep the seeds that fall into this slab, in slab-local coordinates (add_seeds, region.c:450-490:
         only the owning rank takes a seed)"""
         s = np.asarray(seeds_global, np.int64).reshape(-1, 3)
-        keep = (s[:, 2] >= self.z0) & (s[:, 2] < self.z1)
+        a = self.axis
+        keep = (s[:, a] >= self.z0) & (s[:, a] < self.z1)
         loc = s[keep].copy()
-        loc[:, 2] -= self.z0
+        loc[:, a] -= self.z0
         self.nseeds = int(len(loc))
         self.seeds_dev = self.torch.tensor(loc.astype(np.int32).reshape(-1, 3), dtype=self.torch.int32,
                                            device=self.device).contiguous() if self.nseeds else None
@@ -80,7 +88,7 @@ class SlabGrower:
         rank's upper halo (distribute_image_halo, region.c:145-246)"""
         if self.world == 1:
             return
-        dist, plane = self.dist, self.nx * self.ny
+        dist, plane = self.dist, self.plane
         ops = []
         lo_halo = self.buf[:plane]
         hi_halo = self.buf[(self.nzl + 1) * plane:]
@@ -132,9 +140,10 @@ class SlabGrower:
         import os
         self._timing = [] if (os.environ.get("RG_SLAB_TIMING") and self.use_cuda_stream) else None
         self._mark("start")
-        lib, st, plane = self.lib, self._stream(), self.nx * self.ny
+        lib, st, plane = self.lib, self._stream(), self.plane
         slab_ptr = self.buf.data_ptr() + plane
-        self._ck(lib.rg_slab_label(self.ctx, slab_ptr, self.nx, self.ny, self.nzl, int(self.has_lower), int(self.has_upper),
+        ny_l, nz_l = (self.nzl, 1) if self.rows else (self.ny, self.nzl)
+        self._ck(lib.rg_slab_label(self.ctx, slab_ptr, self.nx, ny_l, nz_l, int(self.has_lower), int(self.has_upper),
                                    self.seeds_dev.data_ptr() if self.nseeds else None, self.nseeds, int(threshold),
                                    self.mask.data_ptr(), st), "rg_slab_label")
         self._mark("label")

@@ -60,7 +60,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     Params &P = E.P; memset(&P, 0, sizeof P);
     P.image = image; P.mask = mask; P.nx = nx; P.ny = ny; P.nz = nz;
     P.ntx = (int)((nx + C::TX - 1) / C::TX); P.nty = (int)((ny + C::TY - 1) / C::TY); P.ntz = (int)((nz + C::TZ - 1) / C::TZ);
-    P.zlo_ext = zlo; P.zhi_ext = zhi;
+    P.lo_ext = zlo; P.hi_ext = zhi;
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
     P.mask_prezeroed = g_force_full ? 0 : 1;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
@@ -137,7 +137,11 @@ static int emu_grow_slabs_t(int G, const uint8_t *image, int64_t nx, int64_t ny,
 {
     std::vector<EmuState> E((size_t)G);
     std::vector<int64_t> zb((size_t)G + 1);
-    for (int g = 0; g <= G; g++) zb[(size_t)g] = nz * g / G;
+    /* volumes are cut along z, images (tiles without a z halo) along y */
+    const bool rows = (C::HZ == 0);
+    const int64_t na = rows ? ny : nz, unit = rows ? nx : nx * ny;
+    const int ci = rows ? 1 : 2;
+    for (int g = 0; g <= G; g++) zb[(size_t)g] = na * g / G;
     std::vector<std::vector<int32_t>> sl((size_t)G);
     HostExec ex;
     /* each rank: local seeds (shifted to slab coordinates), pass A + B on its slab */
@@ -145,14 +149,14 @@ static int emu_grow_slabs_t(int G, const uint8_t *image, int64_t nx, int64_t ny,
         int64_t z0 = zb[(size_t)g], z1 = zb[(size_t)g + 1];
         if (z1 <= z0) continue;
         for (int i = 0; i < nseeds; i++) {
-            int32_t z = seeds[3 * i + 2];
-            if (z >= z0 && z < z1) { sl[(size_t)g].push_back(seeds[3 * i]); sl[(size_t)g].push_back(seeds[3 * i + 1]); sl[(size_t)g].push_back((int32_t)(z - z0)); }
+            int32_t t[3] = { seeds[3 * i], seeds[3 * i + 1], seeds[3 * i + 2] };
+            if (t[ci] >= z0 && t[ci] < z1) { t[ci] = (int32_t)(t[ci] - z0); sl[(size_t)g].insert(sl[(size_t)g].end(), t, t + 3); }
         }
         int zlo = 0, zhi = 0;
         for (int h = 0; h < g; h++) if (zb[(size_t)h + 1] > zb[(size_t)h]) zlo = 1;
         for (int h = g + 1; h < G; h++) if (zb[(size_t)h + 1] > zb[(size_t)h]) zhi = 1;
-        emu_setup<C>(E[(size_t)g], image + z0 * nx * ny, nx, ny, z1 - z0, zlo, zhi, sl[(size_t)g].data(), (int)sl[(size_t)g].size() / 3, T,
-                     mask + z0 * nx * ny);
+        emu_setup<C>(E[(size_t)g], image + z0 * unit, nx, rows ? z1 - z0 : ny, rows ? 1 : z1 - z0, zlo, zhi, sl[(size_t)g].data(),
+                     (int)sl[(size_t)g].size() / 3, T, mask + z0 * unit);
         emu_label<C>(E[(size_t)g]);
     }
     /* export interface lists (roots), "all-gather", resolve redundantly, then pass C */
@@ -161,11 +165,11 @@ static int emu_grow_slabs_t(int G, const uint8_t *image, int64_t nx, int64_t ny,
     for (int g = 0; g < G; g++) if (zb[(size_t)g + 1] > zb[(size_t)g]) live.push_back(g);
     for (int g : live) {
         const Params &P = E[(size_t)g].P;
-        size_t cap = (size_t)P.ntx * P.nty * C::FZN + 1;
+        size_t cap = (size_t)iface_tiles<C>(P) * (C::HZ ? C::FZN : C::FYN) + 1;
         lo[(size_t)g].assign(cap, 0); hi[(size_t)g].assign(cap, 0);
         uint32_t nlo = 0, nhi = 0;
-        if (P.zlo_ext) export_interface<C>(ex, P, 0, lo[(size_t)g].data(), &nlo);
-        if (P.zhi_ext) export_interface<C>(ex, P, 1, hi[(size_t)g].data(), &nhi);
+        if (P.lo_ext) export_interface<C>(ex, P, 0, lo[(size_t)g].data(), &nlo);
+        if (P.hi_ext) export_interface<C>(ex, P, 1, hi[(size_t)g].data(), &nhi);
         lo[(size_t)g].resize(nlo); hi[(size_t)g].resize(nhi);
     }
     int rc = 0;
@@ -201,7 +205,9 @@ static int emu_grow_slabs_t(int G, const uint8_t *image, int64_t nx, int64_t ny,
 extern "C" int emu_grow_slabs(int cfg, int G, const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
                               int T, uint8_t *mask, uint32_t *stats)
 {
-    if (nz == 1 || G < 1) return -1;
+    if (G < 1) return -1;
+    if (nz == 1) return cfg == 0 ? emu_grow_slabs_t<Cfg2D>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats)
+                                 : emu_grow_slabs_t<CfgS2>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
     if (cfg == 0) return emu_grow_slabs_t<Cfg3D>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
     if (cfg == 1) return emu_grow_slabs_t<CfgS3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
     return emu_grow_slabs_t<CfgT3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
@@ -213,7 +219,10 @@ static int g_cfg = 1;
 extern "C" void emu_set_cfg(int cfg) { g_cfg = cfg; }
 struct EmuCtx { EmuState E; bool have; int cfg; std::vector<int32_t> seeds; };
 
-#define DISPATCH(cfg, CALL) do { if ((cfg) == 0) { typedef Cfg3D C; CALL; } else if ((cfg) == 1) { typedef CfgS3 C; CALL; } else { typedef CfgT3 C; CALL; } } while (0)
+/* 0 / 1 / 2 = the three volume shapes; 3 / 4 = the two image shapes (chosen by emu_cfg_for when nz_local == 1) */
+#define DISPATCH(cfg, CALL) do { if ((cfg) == 0) { typedef Cfg3D C; CALL; } else if ((cfg) == 1) { typedef CfgS3 C; CALL; } \
+    else if ((cfg) == 2) { typedef CfgT3 C; CALL; } else if ((cfg) == 3) { typedef Cfg2D C; CALL; } else { typedef CfgS2 C; CALL; } } while (0)
+static int emu_cfg_for(int64_t nz_local) { return nz_local == 1 ? (g_cfg == 0 ? 3 : 4) : g_cfg; }
 
 extern "C" int rg_ctx_create(int, void **out) { *out = new EmuCtx(); ((EmuCtx *)*out)->have = false; return 0; }
 extern "C" void rg_ctx_destroy(void *c) { delete (EmuCtx *)c; }
@@ -221,16 +230,17 @@ extern "C" const char *rg_last_error(void) { return "emulator"; }
 extern "C" int rg_slab_label(void *cv, const uint8_t *slab, int64_t nx, int64_t ny, int64_t nzl, int has_lower, int has_upper,
                              const int32_t *seeds, int nseeds, int T, uint8_t *mask, void *)
 {
-    EmuCtx *c = (EmuCtx *)cv; c->cfg = g_cfg;
+    EmuCtx *c = (EmuCtx *)cv; c->cfg = emu_cfg_for(nzl);
     c->seeds.assign(seeds, seeds + 3 * (size_t)nseeds);
     DISPATCH(c->cfg, (emu_setup<C>(c->E, slab, nx, ny, nzl, has_lower, has_upper, c->seeds.data(), nseeds, T, mask), emu_label<C>(c->E)));
     c->have = true;
     return 0;
 }
-extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny)
+extern "C" int64_t rg_slab_interface_capacity(int64_t nx, int64_t ny, int64_t nz_local)
 {
     int64_t r = 0;
-    DISPATCH(g_cfg, (r = ((nx + C::TX - 1) / C::TX) * ((ny + C::TY - 1) / C::TY) * (int64_t)C::FZN));
+    DISPATCH(emu_cfg_for(nz_local), (r = C::HZ ? ((nx + C::TX - 1) / C::TX) * ((ny + C::TY - 1) / C::TY) * (int64_t)C::FZN
+                               : ((nx + C::TX - 1) / C::TX) * (int64_t)C::FYN));
     return r;
 }
 extern "C" int rg_slab_export(void *cv, int side, uint32_t *roots, uint32_t *counts3, void *)
@@ -271,8 +281,8 @@ extern "C" int rg_slab_export_packed(void *cv, uint32_t *packed, uint32_t cap, v
     const Params &P = c->E.P;
     packed[0] = packed[1] = packed[2] = packed[3] = 0;
     for (int side = 0; side < 2; side++) {
-        if (!(side ? P.zhi_ext : P.zlo_ext)) continue;
-        std::vector<uint32_t> off((size_t)P.ntx * P.nty + 1); uint32_t scratch[40];
+        if (!(side ? P.hi_ext : P.lo_ext)) continue;
+        std::vector<uint32_t> off((size_t)P.ntx * P.nty + 1); uint32_t scratch[40];     /* >= iface_tiles + 1 */
         DISPATCH(c->cfg, (export_offsets<C>(ex, P, side, off.data(), packed + side, scratch),
                           export_entries<C>(ex, P, side, off.data(), packed + 4 + (size_t)side * cap, cap)));
     }

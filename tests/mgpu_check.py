@@ -3,7 +3,7 @@
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29700 tests/mgpu_check.py
 
-Every rank labels its z-slab with the CUDA engine, interface lists are all-gathered over NCCL, and the
+Every rank labels its slab (z-slab of a volume, row slab of an image) with the CUDA engine, interface lists are all-gathered over NCCL, and the
 assembled mask is compared byte for byte with the oracle on rank 0 (C4 geometry: the z-serpentine crosses
 every slab interface 64 times; plus a random ragged volume)."""
 import ctypes, os, sys
@@ -31,9 +31,14 @@ def main():
     img = rng.integers(0, 3, size=(61, 70, 208), dtype=np.uint8)
     seeds = np.stack([rng.integers(0, 208, 8), rng.integers(0, 70, 8), rng.integers(0, 61, 8)], 1).astype(np.int32)
     cases.append(("random-ragged", img, seeds, 1))
+    img, seeds, T = ora.synth("c2", 4096, 0x5EED0002); cases.append(("c2-4096-rows", img, seeds, T))      # an image: row slabs
+    img = rng.integers(0, 3, size=(1001, 1040), dtype=np.uint8)
+    seeds = np.stack([rng.integers(0, 1040, 16), rng.integers(0, 1001, 16), np.zeros(16, np.int64)], 1).astype(np.int32)
+    cases.append(("random-image-rows", img, seeds, 1))
     ok = True
     for name, img, seeds, T in cases:
-        nz, ny, nx = img.shape
+        nz, ny, nx = ((1,) + img.shape) if img.ndim == 2 else img.shape
+        na = ny if nz == 1 else nz
         g = rgb200.SlabGrower(lib, ctx.handle, nx, ny, nz, rank, world, dev)
         g.image.copy_(torch.from_numpy(img[g.z0:g.z1]).to(dev))
         g.exchange_image_halos()
@@ -43,8 +48,8 @@ def main():
         assert g.optimistic_steps == 1
         torch.cuda.synchronize()
         st = ctx.status()
-        parts = [torch.empty((rgb200.slab_bounds(nz, r, world)[1] - rgb200.slab_bounds(nz, r, world)[0], ny, nx), dtype=torch.uint8, device=dev)
-                 for r in range(world)]
+        parts = [torch.empty((rgb200.slab_bounds(na, r, world)[1] - rgb200.slab_bounds(na, r, world)[0],) + tuple(m.shape[1:]),
+                             dtype=torch.uint8, device=dev) for r in range(world)]
         dist.all_gather(parts, m.contiguous())
         if rank == 0:
             got = torch.cat(parts).cpu().numpy()

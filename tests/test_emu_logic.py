@@ -111,6 +111,45 @@ def test_emu_slabs_random(emu, oracle, G, cfg):
     assert (got == oracle.grow(img, seeds, 1)).all()
 
 
+@pytest.mark.parametrize("G", [2, 3, 5, 8])
+@pytest.mark.parametrize("cfg,shape", [(1, (37, 70)), (1, (64, 96)), (1, (16, 33)), (0, (300, 272)), (0, (255, 130))])
+@pytest.mark.parametrize("levels,T", [(3, 1), (5, 2)])
+def test_emu_row_slabs_of_an_image(emu, oracle, G, cfg, shape, levels, T):
+    """2-D inputs are cut into ROW slabs (the reference's region.c gives each MPI rank a block of the picture,
+    region.c:106-143): the interface is the YM / YP face row of the first / last tile row, ragged last tile rows
+    (ny % TY != 0) included, one exchange"""
+    rng = np.random.default_rng(abs(hash((G, cfg, shape, levels))) % 2**32)
+    img, seeds = rand_case(rng, shape, levels, 6)
+    got, st = run_emu(emu, cfg, img, seeds, T, slabs=G)
+    assert (got == oracle.grow(img, seeds, T)).all()
+    assert int(st[3]) == G
+
+
+@pytest.mark.parametrize("G", [2, 4, 7])
+def test_emu_row_slabs_snake(emu, oracle, G):
+    """a 1-pixel snake that crosses every row interface many times + the reference picture with its four seeds"""
+    h, w = 64, 96
+    img = np.zeros((h, w), np.uint8)
+    img[:, 1::4] = 200                                    # vertical corridors every 4 columns ...
+    img[0, 1::8] = 0; img[h - 1, 5::8] = 0                # ... alternately closed at the top / bottom
+    for k, x in enumerate(range(1, w - 4, 4)):
+        img[h - 1 if k % 2 == 0 else 0, x:x + 5] = 200    # joined into one snake by turns in the end rows
+    seeds = [[1, 1, 0]]
+    want = oracle.grow(img, seeds, 1)
+    assert want.sum() > 0.2 * h * w
+    got, _ = run_emu(emu, 1, img, seeds, 1, slabs=G)
+    assert (got == want).all()
+
+
+def test_emu_row_slabs_reference_picture(emu, oracle, golden):
+    img = golden["arrays"]["pic1"]
+    seeds = oracle.seeds_2d(512, 512)
+    want = oracle.grow(img, seeds, 2)
+    for G in (2, 4):
+        got, _ = run_emu(emu, 0, img, seeds, 2, slabs=G)
+        assert (got == want).all()
+
+
 @pytest.mark.parametrize("G", [2, 4, 8, 11])
 def test_emu_slabs_serpentine(emu, oracle, G):
     """C4's z-serpentine crosses every slab interface many times: one exchange must be enough"""

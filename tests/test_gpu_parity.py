@@ -216,22 +216,27 @@ def slab_grow_one_device(rg, img, seeds, T, G):
     """run the multi-rank protocol for G logical ranks on one GPU by calling the C ABI phases in turn"""
     import torch
     lib = rg.load_library()
-    nz, ny, nx = img.shape
-    plane = nx * ny
+    rows = img.ndim == 2                                            # an image is cut into row slabs, a volume into z-slabs
+    nz, ny, nx = ((1,) + img.shape) if rows else img.shape
+    plane = nx if rows else nx * ny
+    axis = 1 if rows else 2
     ranks = []
     for r in range(G):
-        z0, z1 = rg.slab_bounds(nz, r, G)
+        z0, z1 = rg.slab_bounds(ny if rows else nz, r, G)
         h = ctypes.c_void_p(); assert lib.rg_ctx_create(0, ctypes.byref(h)) == 0
         buf = torch.zeros((z1 - z0 + 2) * plane, dtype=torch.uint8, device="cuda")
-        lo, hi = max(z0 - 1, 0), min(z1 + 1, nz)
+        lo, hi = max(z0 - 1, 0), min(z1 + 1, ny if rows else nz)
         buf[(lo - z0 + 1) * plane:(hi - z0 + 1) * plane] = torch.from_numpy(img[lo:hi].reshape(-1)).cuda()
         mask = torch.empty((z1 - z0) * plane, dtype=torch.uint8, device="cuda")
-        s = np.asarray([[x, y, z - z0] for x, y, z in np.asarray(seeds).reshape(-1, 3).tolist() if z0 <= z < z1], np.int32).reshape(-1, 3)
-        d_s = torch.from_numpy(s).cuda() if len(s) else None
-        cap = int(lib.rg_slab_interface_capacity(nx, ny))
+        s = np.asarray(seeds, np.int32).reshape(-1, 3)
+        s = s[(s[:, axis] >= z0) & (s[:, axis] < z1)].copy()
+        s[:, axis] -= z0
+        d_s = torch.from_numpy(np.ascontiguousarray(s)).cuda() if len(s) else None
+        cap = int(lib.rg_slab_interface_capacity(nx, ny, 1 if rows else z1 - z0))
         lists = torch.zeros((2, cap), dtype=torch.int32, device="cuda")
         counts = torch.zeros(4, dtype=torch.int32, device="cuda")
-        assert lib.rg_slab_label(h, buf.data_ptr() + plane, nx, ny, z1 - z0, int(r > 0), int(r < G - 1),
+        ny_l, nz_l = (z1 - z0, 1) if rows else (ny, z1 - z0)
+        assert lib.rg_slab_label(h, buf.data_ptr() + plane, nx, ny_l, nz_l, int(r > 0), int(r < G - 1),
                                  d_s.data_ptr() if d_s is not None else None, len(s), T, mask.data_ptr(), None) == 0
         if r > 0:
             assert lib.rg_slab_export(h, 0, lists[0].data_ptr(), counts.data_ptr(), None) == 0
@@ -280,6 +285,43 @@ def test_slabs_random_ragged(rg, ctx, oracle, G):
     img = rng.integers(0, 3, size=(37, 45, 150), dtype=np.uint8)
     seeds = np.stack([rng.integers(0, 150, 6), rng.integers(0, 45, 6), rng.integers(0, 37, 6)], 1)
     assert (slab_grow_one_device(rg, img, seeds, 1, G) == oracle.grow(img, seeds, 1)).all()
+
+
+@pytest.mark.parametrize("G", [2, 3, 8])
+@pytest.mark.parametrize("k", [1, 2, 3, 4])
+def test_row_slabs_reference_pictures(rg, ctx, oracle, golden, G, k):
+    """the reference's own use case (region.c: one picture, several ranks): 512 rows over G ranks do not divide into
+    126-row tiles, so every rank has a ragged last tile row whose YP faces form the interface"""
+    img = golden["arrays"][f"pic{k}"]
+    seeds = oracle.seeds_2d(512, 512)
+    got = slab_grow_one_device(rg, img, seeds, 2, G)
+    assert hashlib.sha256((img * (got == 0)).tobytes()).hexdigest() == golden["pics"][f"pic{k}"]["out_sha256"]
+
+
+@pytest.mark.parametrize("G,shape", [(2, (300, 272)), (5, (1000, 1040)), (4, (37, 48)), (3, (255, 130))])
+def test_row_slabs_random(rg, ctx, oracle, G, shape):
+    """aligned widths (TMA staging) and unaligned ones (generic staging), rows per rank below / above one tile"""
+    rng = np.random.default_rng(60 + G)
+    img = rng.integers(0, 3, size=shape, dtype=np.uint8)
+    h, w = shape
+    seeds = np.stack([rng.integers(0, w, 12), rng.integers(0, h, 12), np.zeros(12, np.int64)], 1)
+    assert (slab_grow_one_device(rg, img, seeds, 1, G) == oracle.grow(img, seeds, 1)).all()
+
+
+def test_row_slabs_c2_snake(rg, ctx, oracle):
+    """C2 geometry (discs and bars on a lattice, some touching) at 2048^2 over 8 row slabs, and a snake that crosses
+    every interface many times"""
+    img, seeds, T = oracle.synth("c2", 2048, 0x5EED0002)
+    assert (slab_grow_one_device(rg, img, seeds, T, 8) == oracle.grow(img, seeds, T)).all()
+    h, w = 512, 768
+    img = np.zeros((h, w), np.uint8)
+    img[:, 1::4] = 200
+    img[0, 1::8] = 0; img[h - 1, 5::8] = 0
+    for k, x in enumerate(range(1, w - 4, 4)):
+        img[h - 1 if k % 2 == 0 else 0, x:x + 5] = 200
+    want = oracle.grow(img, [[1, 1, 0]], 1)
+    assert want.sum() > 0.2 * h * w
+    assert (slab_grow_one_device(rg, img, [[1, 1, 0]], 1, 7) == want).all()
 
 
 def test_apply_mask_device(rg, ctx, oracle, golden):

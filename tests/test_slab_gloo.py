@@ -24,7 +24,7 @@ def _worker(rank, world, port, img, seeds, T, cfg, out_q):
         rgb200.bind(lib, SLAB_FNS)
         lib.emu_set_cfg(cfg)
         h = ctypes.c_void_p(); lib.rg_ctx_create(0, ctypes.byref(h))
-        nz, ny, nx = img.shape
+        nz, ny, nx = ((1,) + img.shape) if img.ndim == 2 else img.shape      # an image is cut into row slabs
         g = rgb200.SlabGrower(lib, h, nx, ny, nz, rank, world, torch.device("cpu"), use_cuda_stream=False)
         g.image.copy_(torch.from_numpy(img[g.z0:g.z1]))
         g.exchange_image_halos()
@@ -83,3 +83,20 @@ def test_slab_grower_gloo_random(oracle):
     seeds = np.stack([rng.integers(0, 70, 6), rng.integers(0, 10, 6), rng.integers(0, 21, 6)], 1).astype(np.int32)
     got = run_world(2, img, seeds, 1, 1, 29613)
     assert (got == oracle.grow(img, seeds, 1)).all()
+
+
+@pytest.mark.parametrize("world,cfg,port", [(2, 1, 29614), (3, 0, 29615)])
+def test_row_slabs_of_an_image_gloo(oracle, golden, world, cfg, port):
+    """2-D input (the reference's own use case, region.c): ranks own row ranges, swap one boundary ROW, one exchange.
+    cfg 0 runs the product's 128x126 image tiles on the reference picture, cfg 1 tiny tiles on a noisy one."""
+    if cfg == 0:
+        img = golden["arrays"]["pic2"]
+        seeds = np.asarray(oracle.seeds_2d(512, 512), np.int32).reshape(-1, 3)
+        T = 2
+    else:
+        rng = np.random.default_rng(5)
+        img = rng.integers(0, 3, size=(45, 100), dtype=np.uint8)
+        seeds = np.stack([rng.integers(0, 100, 8), rng.integers(0, 45, 8), np.zeros(8, np.int64)], 1).astype(np.int32)
+        T = 1
+    got = run_world(world, img, seeds, T, cfg, port)
+    assert (got == oracle.grow(img, seeds, T)).all()
