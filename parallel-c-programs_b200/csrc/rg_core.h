@@ -587,6 +587,9 @@ RG_FN void fill_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t 
 template <class C, class Exec>
 RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0) { fill_tile<C>(ex, P, x0, y0, z0, 0u); }
 
+enum { FLOOD_PLAIN_SWEEPS = 3 };     /* pass C: sweeps with unit stride before the stride planes are built */
+constexpr int ceil_log2(int n) { return n <= 1 ? 0 : 1 + ceil_log2((n + 1) / 2); }
+
 /* shared memory of pass C: staged tile, edge planes, region bits */
 template <class C>
 struct alignas(128) FloodSmem {
@@ -596,6 +599,11 @@ struct alignas(128) FloodSmem {
     alignas(16) uint32_t ey[C::NW];
     alignas(16) uint32_t ez[C::NW];
     alignas(16) uint32_t M[C::NW];                 /* bit i: voxel i is in the region */
+    /* longer strides for the flood: eyk[k-1] bit i = voxel i is linked through 2^k consecutive +y steps (k >= 1;
+       k = 0 is ey itself), ezk likewise in z -- a sweep then carries the region 1, 2, 4, ... rows / planes at once */
+    static constexpr int NLY = ceil_log2(C::TY), NLZ = ceil_log2(C::TZ);
+    alignas(16) uint32_t eyk[NLY > 1 ? NLY - 1 : 1][C::NW];
+    alignas(16) uint32_t ezk[NLZ > 1 ? NLZ - 1 : 1][C::NW];
     uint32_t scal[16];
 };
 
@@ -642,14 +650,18 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     ex.tile_wait(&s.mbar);
     ex.sync();
     if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    if (P.debug_stop == 20) return;
     build_edges<C, false>(ex, P, s.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
     ex.sync();
-    /* every word in parallel: take what the six neighbouring words offer through the edge planes, then close
-       the word's own x-runs; repeat until a sweep changes nothing (a region advances one word per sweep in
-       y and z, a whole run per sweep in x) */
-    bool changed;
-    do {
-        changed = false;
+    if (P.debug_stop == 21) return;
+    /* every word in parallel: take what the neighbouring words offer through the link planes, then close the
+       word's own x-runs; repeat until a sweep changes nothing.  The words race benignly: bits are only ever added,
+       and a sweep that added one is followed by another sweep.  A region advances a whole run per sweep in x but
+       one row / plane per sweep in y and z, so a tile that is still changing after a few sweeps (a solid: up to
+       TY + TZ of them) gets stride planes and continues 1, 2, 4, ... rows and planes at a time. */
+    constexpr int NLY = FloodSmem<C>::NLY, NLZ = FloodSmem<C>::NLZ, NLMAX = NLY > NLZ ? NLY : NLZ;
+    auto sweep = [&](const bool strided) -> bool {
+        bool changed = false;
         ex.pfor(C::NW, [&](int w) {
             const int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
             const uint32_t m = s.M[w], exw = s.ex[w];
@@ -660,6 +672,24 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
                 if (z > 0) in |= s.M[w - C::WX * C::TY] & s.ez[w - C::WX * C::TY];
                 if (z < C::TZ - 1) in |= s.M[w + C::WX * C::TY] & s.ez[w];
             }
+            if (strided) {
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+                for (int k = 1; k < NLY; k++) {
+                    const int d = 1 << k, o = d * C::WX;
+                    if (y >= d) in |= s.M[w - o] & s.eyk[k - 1][w - o];
+                    if (y + d < C::TY) in |= s.M[w + o] & s.eyk[k - 1][w];
+                }
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+                for (int k = 1; k < NLZ; k++) {
+                    const int d = 1 << k, o = d * C::WX * C::TY;
+                    if (z >= d) in |= s.M[w - o] & s.ezk[k - 1][w - o];
+                    if (z + d < C::TZ) in |= s.M[w + o] & s.ezk[k - 1][w];
+                }
+            }
             if (wx > 0) in |= (s.M[w - 1] & s.ex[w - 1]) >> 31;
             if (wx < C::WX - 1) in |= ((s.M[w + 1] & 1u) << 31) & exw;
             if (in) {
@@ -667,7 +697,30 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
                 if (out != m) { s.M[w] = out; changed = true; }
             }
         });
-    } while (ex.sync_or(changed));
+        return ex.sync_or(changed);
+    };
+    bool more = true;
+    for (int i = 0; i < FLOOD_PLAIN_SWEEPS && more; i++) more = sweep(false);
+    if (more) {
+        /* stride planes, one level per barrier: linked over 2h steps = linked over h steps from here and from h further on */
+        for (int k = 1; k < NLMAX; k++) {
+            const int h = 1 << (k - 1);
+            ex.pfor(C::NW, [&](int w) {
+                const int y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+                if (k < NLY) {
+                    const uint32_t *lo = k == 1 ? s.ey : s.eyk[k - 2];
+                    s.eyk[k - 1][w] = (y + h < C::TY) ? (lo[w] & lo[w + h * C::WX]) : 0u;
+                }
+                if (k < NLZ) {
+                    const uint32_t *lo = k == 1 ? s.ez : s.ezk[k - 2];
+                    s.ezk[k - 1][w] = (z + h < C::TZ) ? (lo[w] & lo[w + h * C::WX * C::TY]) : 0u;
+                }
+            });
+            ex.sync();
+        }
+        while (sweep(true)) { }
+    }
+    if (P.debug_stop == 22) return;
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
         int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
         int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;

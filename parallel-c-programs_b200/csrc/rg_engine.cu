@@ -507,11 +507,11 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     c->last_grid = tile_grid;
     k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[2], st);
-    if (!P.debug_stop || P.debug_stop >= 10 && P.debug_stop < 20) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
+    if (!P.debug_stop || P.debug_stop >= 10) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[3], st);
     int64_t items = (int64_t)L.ntiles * MERGE_LANES;                 /* one warp per tile */
     int mb = (int)((items + 255) / 256); if (mb > 148 * 64) mb = 148 * 64;
-    if (!P.debug_stop) k_merge<C><<<mb, 256, 0, st>>>(P);
+    if (!P.debug_stop || P.debug_stop >= 20) k_merge<C><<<mb, 256, 0, st>>>(P);
     if (c->profile) cudaEventRecord(c->ev[4], st);
     CK(cudaGetLastError());
     c->last_counters = P.counters; c->last_stream = st;
@@ -524,7 +524,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
 static int launch_finish(rg_ctx *c, cudaStream_t st)
 {
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
-    if (c->last_P.debug_stop) { if (c->profile) { cudaEventRecord(c->ev[5], st); cudaEventRecord(c->ev[6], st); } return RG_OK; }   /* tuning runs time the fast pass only */
+    if (c->last_P.debug_stop && c->last_P.debug_stop < 20) { if (c->profile) { cudaEventRecord(c->ev[5], st); cudaEventRecord(c->ev[6], st); } return RG_OK; }   /* tuning runs time the fast pass only */
     if (c->last_is2d) {
         k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
