@@ -108,7 +108,7 @@ struct Params {
     uint32_t node_cap;
     uint32_t *complex_list;      /* tiles the fast labelling pass handed to the full one */
     uint32_t *flag_list;         /* tiles that hold part of the region (pass C work list) */
-    int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tile then stores no zeros */
+    int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tiles_all then stores no zeros */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
@@ -571,18 +571,22 @@ RG_FN void merge_faces(Exec &ex, const Params &P)
 }
 
 /* ================================================================ pass C */
+/* one 16-byte chunk of the tile's part of the mask (item = chunk index inside the tile) */
+template <class C>
+RG_FN void fill_chunk(const Params &P, int64_t x0, int64_t y0, int64_t z0, uint32_t byte01, int it)
+{
+    const uint32_t w = byte01 * 0x01010101u;
+    int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+    int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
+    if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
+    uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
+    if (P.fast16) st128_stream(g, u32x4{w, w, w, w});
+    else for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = (uint8_t)byte01;
+}
 template <class C, class Exec>
 RG_FN void fill_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0, uint32_t byte01)
 {
-    const uint32_t w = byte01 * 0x01010101u;
-    ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
-        int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
-        int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
-        if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
-        uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
-        if (P.fast16) st128_stream(g, u32x4{w, w, w, w});
-        else for (int b = 0; b < 16 && gx + b < P.nx; b++) g[b] = (uint8_t)byte01;
-    });
+    ex.pfor(C::TZ * C::TY * C::CX, [&](int it) { fill_chunk<C>(P, x0, y0, z0, byte01, it); });
 }
 template <class C, class Exec>
 RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0) { fill_tile<C>(ex, P, x0, y0, z0, 0u); }

@@ -79,6 +79,15 @@ struct DevExec {
     {
         for (int i = (int)threadIdx.x; i < n; i += NT) f(i);
     }
+    /* one warp per item: pred(item, lane) is OR-ed over the warp and handed to body(item, lane, any) */
+    template <class Pr, class Bo> __device__ __forceinline__ void wfor(uint32_t n, Pr pred, Bo body)
+    {
+        const uint32_t lane = threadIdx.x & 31u, wpb = NT / 32;
+        for (uint32_t item = blockIdx.x * wpb + (threadIdx.x >> 5); item < n; item += gridDim.x * wpb) {
+            const bool any = __any_sync(0xFFFFFFFFu, pred(item, lane));
+            body(item, lane, any);
+        }
+    }
     template <class F> __device__ __forceinline__ void gpfor(int64_t n, F f)
     {
         for (int64_t i = (int64_t)blockIdx.x * NT + threadIdx.x; i < n; i += (int64_t)gridDim.x * NT) f(i);
@@ -128,7 +137,7 @@ struct DevExec {
 #ifndef RG_FAST_THREADS
 #define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (68 KB smem each) */
 #endif
-#define RG_FLAG_THREADS 128     /* flag / zero-fill: no smem */
+#define RG_FLAG_THREADS 256     /* flag / zero-fill: no smem, 8 tiles per CTA */
 #define RG_PERSISTENT_CTAS (148 * 2)
 
 /* pass A, fast path: every tile */
@@ -160,14 +169,12 @@ __global__ void __launch_bounds__(RG_THREADS, RG_FULL_MINB) k_pass_a_full(const 
     pass_a_full_list<C>(ex, P, s);
 }
 
-/* pass C, part 1: zero-fill tiles without region voxels, list the others */
+/* pass C, part 1: zero-fill tiles without region voxels, list the others (one warp per tile) */
 template <class C>
 __global__ void __launch_bounds__(RG_FLAG_THREADS) k_flag_tiles(const Params P)
 {
     DevExec<RG_FLAG_THREADS> ex;
-    ex.grid3d = gridDim.y * gridDim.z > 1 || (P.nty == 1 && P.ntz == 1);
-    const uint32_t tile = ex.grid3d ? (blockIdx.z * (uint32_t)P.nty + blockIdx.y) * (uint32_t)P.ntx + blockIdx.x : blockIdx.x;
-    flag_tile<C>(ex, P, tile);
+    flag_tiles_all<C>(ex, P);
 }
 
 /* pass C, part 2: the listed tiles (persistent CTAs) */
@@ -461,6 +468,12 @@ static int set_attrs()
 }
 
 /* ------------------------------------------------------------------ the launch sequence */
+static unsigned flag_blocks(uint32_t ntiles)        /* one warp per tile, grid-stride beyond 32 CTAs per SM */
+{
+    const unsigned wpb = RG_FLAG_THREADS / 32, b = (ntiles + wpb - 1) / wpb;
+    return b < 1 ? 1 : b > 148u * 32u ? 148u * 32u : b;
+}
+
 template <class C>
 static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
                        int lo_ext, int hi_ext, const int32_t *d_seeds, int nseeds, int threshold,
@@ -526,11 +539,11 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
     if (!c->have_last) return fail(RG_ERR_ARG, "finish without a label pass");
     if (c->last_P.debug_stop && c->last_P.debug_stop < 20) { if (c->profile) { cudaEventRecord(c->ev[5], st); cudaEventRecord(c->ev[6], st); } return RG_OK; }   /* tuning runs time the fast pass only */
     if (c->last_is2d) {
-        k_flag_tiles<Cfg2D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_flag_tiles<Cfg2D><<<flag_blocks(c->last_ntiles), RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
         k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
     } else {
-        k_flag_tiles<Cfg3D><<<c->last_grid, RG_FLAG_THREADS, 0, st>>>(c->last_P);
+        k_flag_tiles<Cfg3D><<<flag_blocks(c->last_ntiles), RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
         k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
     }

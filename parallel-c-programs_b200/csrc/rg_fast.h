@@ -15,7 +15,7 @@
  *                     into dense node ids, so nodes and face lists come out as in rg_core.h.  A tile in
  *                     which any walk overflows (a solid's surface, a corridor ...) is appended to a work
  *                     list and labelled by the full pass instead; nothing but zeros is written for it here.
- *   flag_tile         one small CTA per tile, no smem: decides whether any node of the tile ended up in the
+ *   flag_tiles_all    one warp per tile, no smem: decides whether any node of the tile ended up in the
  *                     region (root == node 0).  Uniform region tiles are filled with ones, the other region
  *                     tiles are appended to the pass C work list; empty tiles were cleared by the fast pass.
  *
@@ -344,20 +344,30 @@ RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
 }
 
 /* ================================================================ region tiles vs. empty tiles */
+/* One warp per tile (a tile has a few hundred nodes at most; a CTA per tile spends its time being scheduled):
+ * does any node of the tile hang under node 0?  Then a uniform tile is filled with ones on the spot and any other
+ * tile goes to the list of pass C; a tile without region voxels is cleared here unless the labelling pass did that. */
+enum { FLAG_LANES = 32 };
 template <class C, class Exec>
-RG_FN void flag_tile(Exec &ex, const Params &P, uint32_t tile)
+RG_FN void flag_tiles_all(Exec &ex, const Params &P)
 {
-    int tx, ty, tz; ex.template origin<C>(P, tile, tx, ty, tz);
-    const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
-    const TileRec rc = P.rec[tile];
-    bool mine = false;
-    ex.pfor((int)rc.nnodes, [&](int i) { if (find32(P.nparent, rc.node_base + (uint32_t)i) == 0u) mine = true; });
-    if (ex.sync_or(mine)) {
-        if (rc.uniform) { fill_tile<C>(ex, P, x0, y0, z0, 1u); return; }      /* whole tile is one region component */
-        if (ex.tid() == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
-        return;
-    }
-    if (!P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);
+    const uint32_t ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
+    ex.wfor(ntiles,
+        [&](uint32_t tile, uint32_t lane) -> bool {
+            const uint32_t nn = P.rec[tile].nnodes, nb = P.rec[tile].node_base;
+            for (uint32_t i = lane; i < nn; i += FLAG_LANES) if (find32(P.nparent, nb + i) == 0u) return true;
+            return false;
+        },
+        [&](uint32_t tile, uint32_t lane, bool mine) {
+            if (mine && !P.rec[tile].uniform) {
+                if (lane == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
+                return;
+            }
+            if (!mine && P.mask_prezeroed) return;
+            int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+            const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
+            for (int it = (int)lane; it < C::TZ * C::TY * C::CX; it += FLAG_LANES) fill_chunk<C>(P, x0, y0, z0, mine ? 1u : 0u, it);
+        });
 }
 
 template <class C, class Exec>

@@ -23,6 +23,14 @@ struct HostExec {
     int tid() const { return 0; }
     template <class F> void pfor(int n, F f) { for (int i = 0; i < n; i++) f(i); }
     template <class F> void gpfor(int64_t n, F f) { for (int64_t i = 0; i < n; i++) f(i); }
+    template <class Pr, class Bo> void wfor(uint32_t n, Pr pred, Bo body)
+    {
+        for (uint32_t item = 0; item < n; item++) {
+            bool any = false;
+            for (uint32_t lane = 0; lane < 32; lane++) any = pred(item, lane) || any;
+            for (uint32_t lane = 0; lane < 32; lane++) body(item, lane, any);
+        }
+    }
     void sync() {}
     bool sync_or(bool p) { return p; }
     template <class C> bool tma_tile(const Params &, uint8_t *, uint64_t *, int64_t, int64_t, int64_t) { return false; }
@@ -94,9 +102,8 @@ template <class C> static void emu_label(EmuState &E)
 template <class C> static void emu_finish(EmuState &E)
 {
     HostExec ex; const Params &P = E.P;
-    uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
     FloodSmem<C> *s = (FloodSmem<C> *)aligned_alloc(128, (sizeof(FloodSmem<C>) + 127) / 128 * 128);
-    for (uint32_t t = 0; t < ntiles; t++) flag_tile<C>(ex, P, t);
+    flag_tiles_all<C>(ex, P);
     memset(s, 0x5A, sizeof *s);
     pass_c_list<C>(ex, P, *s);
     free(s);
