@@ -137,12 +137,15 @@ struct DevExec {
 #ifndef RG_FAST_THREADS
 #define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (68 KB smem each) */
 #endif
+#ifndef RG_FAST_MINB
+#define RG_FAST_MINB 3
+#endif
 #define RG_FLAG_THREADS 256     /* flag / zero-fill: no smem, 8 tiles per CTA */
 #define RG_PERSISTENT_CTAS (148 * 2)
 
 /* pass A, fast path: every tile */
 template <class C>
-__global__ void __launch_bounds__(RG_FAST_THREADS, 3) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap)
+__global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     FastSmem<C> &s = *reinterpret_cast<FastSmem<C> *>(smem_raw);
