@@ -125,6 +125,17 @@ typedef uint16_t parent_t;
 #endif
 
 /* ---------------------------------------------------------------- shared-memory tile state */
+constexpr int ceil_log2(int n) { return n <= 1 ? 0 : 1 + ceil_log2((n + 1) / 2); }
+
+/* longer strides for the flood: eyk[k-1] bit i = voxel i is linked through 2^k consecutive +y steps (k >= 1;
+   k = 0 is the ey plane itself), ezk likewise in z -- a sweep then carries a set 1, 2, 4, ... rows / planes at once */
+template <class C>
+struct StridePlanes {
+    static constexpr int NLY = ceil_log2(C::TY), NLZ = ceil_log2(C::TZ);
+    alignas(16) uint32_t eyk[NLY > 1 ? NLY - 1 : 1][C::NW];
+    alignas(16) uint32_t ezk[NLZ > 1 ? NLZ - 1 : 1][C::NW];
+};
+
 template <class C>
 struct alignas(128) TileSmem {
     union alignas(128) U {
@@ -360,6 +371,95 @@ RG_FN void build_edges(Exec &ex, const Params &P, const uint8_t *img, uint32_t *
     });
 }
 
+/* ---------------------------------------------------------------- bit-parallel flood inside a tile
+   (pass C floods the region from its representatives) */
+enum { FLOOD_PLAIN_SWEEPS = 3 };     /* pass C: sweeps with unit stride before the stride planes are built */
+
+/* all voxels reachable from the set bits of s along the links of A (bit i: voxel i linked to i+1), inside
+   one 32-voxel word: a carry runs from each seed to the end of its run (upwards), and the same on the
+   bit-reversed word (downwards) */
+RG_FN uint32_t fill_up(uint32_t s, uint32_t A) { return ((A + (s & A)) ^ A) | s; }
+#if RG_DEVICE_BUILD
+RG_FN uint32_t brev32(uint32_t x) { return __brev(x); }
+#else
+RG_FN uint32_t brev32(uint32_t x) { uint32_t r = 0; for (int i = 0; i < 32; i++) if ((x >> i) & 1u) r |= 1u << (31 - i); return r; }
+#endif
+RG_FN uint32_t fill_word(uint32_t s, uint32_t A)
+{
+    A &= 0x7FFFFFFFu;
+    return fill_up(s, A) | brev32(fill_up(brev32(s), brev32(A) >> 1));
+}
+
+/* one level per barrier: linked over 2h steps = linked over h steps from here and from h further on */
+template <class C, class Exec>
+RG_FN void build_stride_planes(Exec &ex, const uint32_t *pey, const uint32_t *pez, StridePlanes<C> &sp)
+{
+    constexpr int NLY = StridePlanes<C>::NLY, NLZ = StridePlanes<C>::NLZ, NLMAX = NLY > NLZ ? NLY : NLZ;
+    for (int k = 1; k < NLMAX; k++) {
+        const int h = 1 << (k - 1);
+        ex.pfor(C::NW, [&](int w) {
+            const int y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+            if (k < NLY) {
+                const uint32_t *lo = k == 1 ? pey : sp.eyk[k - 2];
+                sp.eyk[k - 1][w] = (y + h < C::TY) ? (lo[w] & lo[w + h * C::WX]) : 0u;
+            }
+            if (k < NLZ) {
+                const uint32_t *lo = k == 1 ? pez : sp.ezk[k - 2];
+                sp.ezk[k - 1][w] = (z + h < C::TZ) ? (lo[w] & lo[w + h * C::WX * C::TY]) : 0u;
+            }
+        });
+        ex.sync();
+    }
+}
+
+/* One sweep over the words of M (bit i: voxel i belongs to the set): take what the neighbouring words offer through
+   the link planes -- with `strided` also the words 2, 4, ... rows and planes away -- then close the word's own
+   x-runs.  The words race benignly: bits are only ever added, and a sweep that added one reports it, so the caller
+   sweeps again.  Ends with a barrier; returns whether any word changed. */
+template <class C, class Exec>
+RG_FN bool flood_sweep(Exec &ex, uint32_t *M, const uint32_t *pex, const uint32_t *pey, const uint32_t *pez,
+                       const StridePlanes<C> &sp, const bool strided)
+{
+    constexpr int NLY = StridePlanes<C>::NLY, NLZ = StridePlanes<C>::NLZ;
+    bool changed = false;
+    ex.pfor(C::NW, [&](int w) {
+        const int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
+        const uint32_t m = M[w], exw = pex[w];
+        uint32_t in = m;
+        if (y > 0) in |= M[w - C::WX] & pey[w - C::WX];
+        if (y < C::TY - 1) in |= M[w + C::WX] & pey[w];
+        if (C::HZ) {
+            if (z > 0) in |= M[w - C::WX * C::TY] & pez[w - C::WX * C::TY];
+            if (z < C::TZ - 1) in |= M[w + C::WX * C::TY] & pez[w];
+        }
+        if (strided) {
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+            for (int k = 1; k < NLY; k++) {
+                const int d = 1 << k, o = d * C::WX;
+                if (y >= d) in |= M[w - o] & sp.eyk[k - 1][w - o];
+                if (y + d < C::TY) in |= M[w + o] & sp.eyk[k - 1][w];
+            }
+#if RG_DEVICE_BUILD
+#pragma unroll
+#endif
+            for (int k = 1; k < NLZ; k++) {
+                const int d = 1 << k, o = d * C::WX * C::TY;
+                if (z >= d) in |= M[w - o] & sp.ezk[k - 1][w - o];
+                if (z + d < C::TZ) in |= M[w + o] & sp.ezk[k - 1][w];
+            }
+        }
+        if (wx > 0) in |= (M[w - 1] & pex[w - 1]) >> 31;
+        if (wx < C::WX - 1) in |= ((M[w + 1] & 1u) << 31) & exw;
+        if (in) {
+            const uint32_t out = fill_word(in, exw);
+            if (out != m) { M[w] = out; changed = true; }
+        }
+    });
+    return ex.sync_or(changed);
+}
+
 /* ---------------------------------------------------------------- run-based union-find inside the tile */
 template <class C, class Exec>
 RG_FN void label_runs(Exec &ex, TileSmem<C> &s)
@@ -591,9 +691,6 @@ RG_FN void fill_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t 
 template <class C, class Exec>
 RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t z0) { fill_tile<C>(ex, P, x0, y0, z0, 0u); }
 
-enum { FLOOD_PLAIN_SWEEPS = 3 };     /* pass C: sweeps with unit stride before the stride planes are built */
-constexpr int ceil_log2(int n) { return n <= 1 ? 0 : 1 + ceil_log2((n + 1) / 2); }
-
 /* shared memory of pass C: staged tile, edge planes, region bits */
 template <class C>
 struct alignas(128) FloodSmem {
@@ -603,28 +700,9 @@ struct alignas(128) FloodSmem {
     alignas(16) uint32_t ey[C::NW];
     alignas(16) uint32_t ez[C::NW];
     alignas(16) uint32_t M[C::NW];                 /* bit i: voxel i is in the region */
-    /* longer strides for the flood: eyk[k-1] bit i = voxel i is linked through 2^k consecutive +y steps (k >= 1;
-       k = 0 is ey itself), ezk likewise in z -- a sweep then carries the region 1, 2, 4, ... rows / planes at once */
-    static constexpr int NLY = ceil_log2(C::TY), NLZ = ceil_log2(C::TZ);
-    alignas(16) uint32_t eyk[NLY > 1 ? NLY - 1 : 1][C::NW];
-    alignas(16) uint32_t ezk[NLZ > 1 ? NLZ - 1 : 1][C::NW];
+    StridePlanes<C> sp;
     uint32_t scal[16];
 };
-
-/* all voxels reachable from the set bits of s along the links of A (bit i: voxel i linked to i+1), inside
-   one 32-voxel word: a carry runs from each seed to the end of its run (upwards), and the same on the
-   bit-reversed word (downwards) */
-RG_FN uint32_t fill_up(uint32_t s, uint32_t A) { return ((A + (s & A)) ^ A) | s; }
-#if RG_DEVICE_BUILD
-RG_FN uint32_t brev32(uint32_t x) { return __brev(x); }
-#else
-RG_FN uint32_t brev32(uint32_t x) { uint32_t r = 0; for (int i = 0; i < 32; i++) if ((x >> i) & 1u) r |= 1u << (31 - i); return r; }
-#endif
-RG_FN uint32_t fill_word(uint32_t s, uint32_t A)
-{
-    A &= 0x7FFFFFFFu;
-    return fill_up(s, A) | brev32(fill_up(brev32(s), brev32(A) >> 1));
-}
 
 template <class C, class Exec>
 RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s)
@@ -658,71 +736,14 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     build_edges<C, false>(ex, P, s.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 21) return;
-    /* every word in parallel: take what the neighbouring words offer through the link planes, then close the
-       word's own x-runs; repeat until a sweep changes nothing.  The words race benignly: bits are only ever added,
-       and a sweep that added one is followed by another sweep.  A region advances a whole run per sweep in x but
-       one row / plane per sweep in y and z, so a tile that is still changing after a few sweeps (a solid: up to
-       TY + TZ of them) gets stride planes and continues 1, 2, 4, ... rows and planes at a time. */
-    constexpr int NLY = FloodSmem<C>::NLY, NLZ = FloodSmem<C>::NLZ, NLMAX = NLY > NLZ ? NLY : NLZ;
-    auto sweep = [&](const bool strided) -> bool {
-        bool changed = false;
-        ex.pfor(C::NW, [&](int w) {
-            const int wx = w % C::WX, y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
-            const uint32_t m = s.M[w], exw = s.ex[w];
-            uint32_t in = m;
-            if (y > 0) in |= s.M[w - C::WX] & s.ey[w - C::WX];
-            if (y < C::TY - 1) in |= s.M[w + C::WX] & s.ey[w];
-            if (C::HZ) {
-                if (z > 0) in |= s.M[w - C::WX * C::TY] & s.ez[w - C::WX * C::TY];
-                if (z < C::TZ - 1) in |= s.M[w + C::WX * C::TY] & s.ez[w];
-            }
-            if (strided) {
-#if RG_DEVICE_BUILD
-#pragma unroll
-#endif
-                for (int k = 1; k < NLY; k++) {
-                    const int d = 1 << k, o = d * C::WX;
-                    if (y >= d) in |= s.M[w - o] & s.eyk[k - 1][w - o];
-                    if (y + d < C::TY) in |= s.M[w + o] & s.eyk[k - 1][w];
-                }
-#if RG_DEVICE_BUILD
-#pragma unroll
-#endif
-                for (int k = 1; k < NLZ; k++) {
-                    const int d = 1 << k, o = d * C::WX * C::TY;
-                    if (z >= d) in |= s.M[w - o] & s.ezk[k - 1][w - o];
-                    if (z + d < C::TZ) in |= s.M[w + o] & s.ezk[k - 1][w];
-                }
-            }
-            if (wx > 0) in |= (s.M[w - 1] & s.ex[w - 1]) >> 31;
-            if (wx < C::WX - 1) in |= ((s.M[w + 1] & 1u) << 31) & exw;
-            if (in) {
-                const uint32_t out = fill_word(in, exw);
-                if (out != m) { s.M[w] = out; changed = true; }
-            }
-        });
-        return ex.sync_or(changed);
-    };
+    /* A region advances a whole run per sweep in x but one row / plane per sweep in y and z, so a tile that is still
+       changing after a few sweeps (a solid: up to TY + TZ of them) gets stride planes and continues 1, 2, 4, ...
+       rows and planes at a time. */
     bool more = true;
-    for (int i = 0; i < FLOOD_PLAIN_SWEEPS && more; i++) more = sweep(false);
+    for (int i = 0; i < FLOOD_PLAIN_SWEEPS && more; i++) more = flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.sp, false);
     if (more) {
-        /* stride planes, one level per barrier: linked over 2h steps = linked over h steps from here and from h further on */
-        for (int k = 1; k < NLMAX; k++) {
-            const int h = 1 << (k - 1);
-            ex.pfor(C::NW, [&](int w) {
-                const int y = (w / C::WX) % C::TY, z = w / (C::WX * C::TY);
-                if (k < NLY) {
-                    const uint32_t *lo = k == 1 ? s.ey : s.eyk[k - 2];
-                    s.eyk[k - 1][w] = (y + h < C::TY) ? (lo[w] & lo[w + h * C::WX]) : 0u;
-                }
-                if (k < NLZ) {
-                    const uint32_t *lo = k == 1 ? s.ez : s.ezk[k - 2];
-                    s.ezk[k - 1][w] = (z + h < C::TZ) ? (lo[w] & lo[w + h * C::WX * C::TY]) : 0u;
-                }
-            });
-            ex.sync();
-        }
-        while (sweep(true)) { }
+        build_stride_planes<C>(ex, s.ey, s.ez, s.sp);
+        while (flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.sp, true)) { }
     }
     if (P.debug_stop == 22) return;
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {

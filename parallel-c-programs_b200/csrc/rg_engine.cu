@@ -156,6 +156,10 @@ __global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(c
     tile_pass_a_fast<C>(ex, P, tile, s);
 }
 
+static_assert(sizeof(TileSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2 && sizeof(FloodSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2,
+              "the persistent passes are sized for two CTAs per SM");
+static_assert(3 * (sizeof(FastSmem<Cfg3D>) + 1024) <= 227 * 1024, "the fast labelling pass is sized for three CTAs per SM");
+
 /* pass A, full path: the tiles the fast path listed (persistent CTAs) */
 #ifdef RG_PARENT32
 #define RG_FULL_MINB 1
@@ -310,6 +314,22 @@ static int fail(int code, const char *what, cudaError_t e = cudaSuccess)
 }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(RG_ERR_CUDA, #call, e_); } while (0)
 
+/* The entry points run on the context's device and leave the caller's current device as they found it
+   (a host with several contexts in one thread must not find itself on another GPU after a call). */
+struct DeviceScope {
+    int prev; cudaError_t err;
+    explicit DeviceScope(int dev) : prev(-1)
+    {
+        int cur = -1;
+        err = cudaGetDevice(&cur);
+        if (err == cudaSuccess && cur != dev) { err = cudaSetDevice(dev); if (err == cudaSuccess) prev = cur; }
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceScope(const DeviceScope &) = delete;
+    DeviceScope &operator=(const DeviceScope &) = delete;
+};
+#define ON_DEVICE(dev) DeviceScope device_scope_(dev); CK(device_scope_.err)
+
 extern "C" const char *rg_last_error(void) { return g_err; }
 
 /* ------------------------------------------------------------------ context */
@@ -422,7 +442,7 @@ extern "C" int rg_ctx_create(int device, rg_ctx **out)
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return fail(RG_ERR_CUDA, "no CUDA device (this library has no CPU path)", e);
     if (device < 0 || device >= ndev) return fail(RG_ERR_ARG, "bad device index");
-    CK(cudaSetDevice(device));
+    ON_DEVICE(device);
     rg_ctx *c = (rg_ctx *)calloc(1, sizeof(rg_ctx));
     if (!c) return fail(RG_ERR_NOMEM, "calloc");
     c->device = device;
@@ -435,7 +455,7 @@ extern "C" int rg_ctx_create(int device, rg_ctx **out)
 extern "C" void rg_ctx_destroy(rg_ctx *c)
 {
     if (!c) return;
-    cudaSetDevice(c->device);
+    DeviceScope scope(c->device);
     cudaFree(c->ws); cudaFree(c->d_image); cudaFree(c->d_mask); cudaFree(c->d_seeds);
     cudaFreeHost(c->h_status);
     if (c->ev_made) for (int i = 0; i < 7; i++) cudaEventDestroy(c->ev[i]);
@@ -445,7 +465,7 @@ extern "C" void rg_ctx_destroy(rg_ctx *c)
 static int ensure_ws(rg_ctx *c, size_t bytes)
 {
     if (bytes <= c->ws_bytes) return RG_OK;
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (c->ws) { CK(cudaDeviceSynchronize()); cudaFree(c->ws); c->ws = nullptr; c->ws_bytes = 0; }
     cudaError_t e = cudaMalloc(&c->ws, bytes);
     if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(workspace)", e);
@@ -561,7 +581,7 @@ static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int6
 {
     if (!c || !d_image || !d_mask || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !d_seeds))
         return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (!c->attr_set) {
         int rc = set_attrs<Cfg3D>(); if (rc) return rc;
         rc = set_attrs<Cfg2D>(); if (rc) return rc;
@@ -619,7 +639,7 @@ static void export_side(rg_ctx *c, int side, uint32_t *d_count, uint32_t *d_root
 extern "C" int rg_slab_export(rg_ctx *c, int side, uint32_t *d_roots_out, uint32_t *d_counts3, void *stream)
 {
     if (!c || !c->have_last || !d_roots_out || !d_counts3 || side < 0 || side > 1) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     export_side(c, side, d_counts3 + side, d_roots_out, d_counts3, 0xFFFFFFFFu, (cudaStream_t)stream);
     CK(cudaGetLastError());
     return RG_OK;
@@ -630,7 +650,7 @@ static int blocks_for(uint32_t n) { int b = (int)((n + 255u) / 256u); return b <
 extern "C" int rg_slab_resolve_init(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_roots, uint32_t n, uint32_t vertex_offset, void *stream)
 {
     if (!c || !d_xpar || (n && !d_roots)) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     k_resolve_init<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(d_xpar, d_roots, n, vertex_offset);
     CK(cudaGetLastError());
     return RG_OK;
@@ -640,7 +660,7 @@ extern "C" int rg_slab_resolve_union(rg_ctx *c, uint32_t *d_xpar, const uint32_t
                                      const uint32_t *d_lower_of_upper_rank, uint32_t off_upper_rank, uint32_t n, void *stream)
 {
     if (!c || !d_xpar || (n && (!d_upper_of_lower_rank || !d_lower_of_upper_rank))) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (!n) return RG_OK;
     k_resolve_union<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(d_xpar, d_upper_of_lower_rank, off_lower_rank, d_lower_of_upper_rank, off_upper_rank, n);
     CK(cudaGetLastError());
@@ -650,7 +670,7 @@ extern "C" int rg_slab_resolve_union(rg_ctx *c, uint32_t *d_xpar, const uint32_t
 extern "C" int rg_slab_resolve_apply(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_own_roots, uint32_t n, uint32_t own_vertex_offset, void *stream)
 {
     if (!c || !c->have_last || !d_xpar || (n && !d_own_roots)) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (!n) return RG_OK;
     k_resolve_apply<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(c->last_P, d_xpar, d_own_roots, n, own_vertex_offset);
     CK(cudaGetLastError());
@@ -662,7 +682,7 @@ extern "C" int rg_slab_resolve(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_li
 {
     if (!c || !c->have_last || !d_xpar || !d_lists || !counts4 || world < 2 || world > RESOLVE_MAX_RANKS || rank < 0 || rank >= world || !stride)
         return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     ResolveArgs A; memset(&A, 0, sizeof A);
     A.world = (uint32_t)world; A.rank = (uint32_t)rank; A.stride = stride;
     uint64_t off = 1;
@@ -685,7 +705,7 @@ extern "C" int rg_slab_resolve(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_li
 extern "C" int rg_slab_export_packed(rg_ctx *c, uint32_t *d_packed, uint32_t cap, void *stream)
 {
     if (!c || !c->have_last || !d_packed || !cap) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
     const Params &P = c->last_P;
     CK(cudaMemsetAsync(d_packed, 0, 16, st));
@@ -702,7 +722,7 @@ extern "C" int rg_slab_resolve_packed(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar
 {
     if (!c || !c->have_last || !d_xpar || !d_packed_all || !cap || world < 2 || world > RESOLVE_MAX_RANKS || rank < 0 || rank >= world)
         return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
     const uint32_t stride = 4u + 2u * cap;
     k_resolve_prepare<<<1, 32, 0, st>>>(c->last_P, d_packed_all, stride, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, c->d_rargs, d_xpar);
@@ -716,7 +736,7 @@ extern "C" int rg_slab_resolve_packed(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar
 extern "C" int rg_slab_finish(rg_ctx *c, void *stream)
 {
     if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     return launch_finish(c, (cudaStream_t)stream);
 }
 
@@ -729,7 +749,7 @@ extern "C" int rg_grow_device(rg_ctx *c, const uint8_t *d_image, int64_t nx, int
 extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
 {
     if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (!c->last_counters) { if (stats) memset(stats, 0, 16); return RG_OK; }
     CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
     CK(cudaStreamSynchronize(c->last_stream));
@@ -744,7 +764,7 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
 extern "C" int rg_ctx_profile(rg_ctx *c, int enable)
 {
     if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (enable && !c->ev_made) { for (int i = 0; i < 7; i++) CK(cudaEventCreate(&c->ev[i])); c->ev_made = true; }
     c->profile = enable != 0;
     return RG_OK;
@@ -753,7 +773,7 @@ extern "C" int rg_ctx_profile(rg_ctx *c, int enable)
 extern "C" int rg_ctx_profile_read(rg_ctx *c, float ms[6])
 {
     if (!c || !ms || !c->ev_made) return fail(RG_ERR_ARG, "profiling was not enabled");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     CK(cudaEventSynchronize(c->ev[6]));
     for (int i = 0; i < 6; i++) CK(cudaEventElapsedTime(&ms[i], c->ev[i], c->ev[i + 1]));
     return RG_OK;
@@ -762,7 +782,7 @@ extern "C" int rg_ctx_profile_read(rg_ctx *c, float ms[6])
 extern "C" int rg_apply_mask_device(rg_ctx *c, uint8_t *d_image, const uint8_t *d_mask, int64_t n, void *stream)
 {
     if (!c || !d_image || !d_mask || n < 0) return fail(RG_ERR_ARG, "bad argument");
-    CK(cudaSetDevice(c->device));
+    ON_DEVICE(c->device);
     if (n == 0) return RG_OK;
     int64_t b = (n + 255) / 256; if (b > 148 * 32) b = 148 * 32;
     k_apply_mask<<<(int)b, 256, 0, (cudaStream_t)stream>>>(d_image, d_mask, n);

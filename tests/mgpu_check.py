@@ -57,6 +57,21 @@ def main():
             same = bool((got == want).all())
             ok = ok and same
             print(f"{name}: world={world} parity={'OK' if same else 'MISMATCH'} region={int(want.sum())} status={st}", flush=True)
+    # a context on ANOTHER device than the current one: the call must run there and leave the current device alone
+    other = (local + 1) % torch.cuda.device_count()
+    if other != local:
+        rng = np.random.default_rng(9)
+        img = rng.integers(0, 3, size=(20, 40, 80), dtype=np.uint8)
+        seeds = np.array([[3, 3, 3], [70, 30, 15]], np.int32)
+        octx = rgb200.Context(other)
+        d_img = torch.from_numpy(img).to(f"cuda:{other}"); d_seeds = torch.from_numpy(seeds).to(f"cuda:{other}")
+        d_out = torch.empty_like(d_img)
+        octx.grow(d_img, d_seeds, 1, d_out, stream=torch.cuda.current_stream(other).cuda_stream)
+        torch.cuda.synchronize(other)
+        same = bool((d_out.cpu().numpy() == ora.grow(img, seeds, 1)).all()) and torch.cuda.current_device() == local
+        print(f"rank {rank}: context on cuda:{other} while current device is cuda:{local}: {'OK' if same else 'MISMATCH'}", flush=True)
+        ok_t = torch.tensor([1 if same else 0], device=dev); dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+        ok = ok and bool(ok_t.item())
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0 and not ok:
