@@ -373,7 +373,10 @@ RG_FN void build_edges(Exec &ex, const Params &P, const uint8_t *img, uint32_t *
 
 /* ---------------------------------------------------------------- bit-parallel flood inside a tile
    (pass C floods the region from its representatives) */
-enum { FLOOD_PLAIN_SWEEPS = 3 };     /* pass C: sweeps with unit stride before the stride planes are built */
+#ifndef RG_FLOOD_PLAIN
+#define RG_FLOOD_PLAIN 3
+#endif
+enum { FLOOD_PLAIN_SWEEPS = RG_FLOOD_PLAIN };     /* pass C: sweeps with unit stride before the stride planes are built */
 
 /* all voxels reachable from the set bits of s along the links of A (bit i: voxel i linked to i+1), inside
    one 32-voxel word: a carry runs from each seed to the end of its run (upwards), and the same on the
