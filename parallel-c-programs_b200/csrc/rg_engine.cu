@@ -598,6 +598,8 @@ static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int6
 static int grow_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz, int lo_ext, int hi_ext,
                             const int32_t *d_seeds, int nseeds, int threshold, uint8_t *d_mask, void *stream)
 {
+    if (!c) return fail(RG_ERR_ARG, "ctx == NULL");
+    ON_DEVICE(c->device);                                   /* both halves run on the context's device */
     int rc = label_device_impl(c, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, stream);
     if (rc) return rc;
     return launch_finish(c, (cudaStream_t)stream);
