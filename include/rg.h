@@ -73,7 +73,9 @@ int rg_grow(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
 int rg_ctx_create(int device, rg_ctx **out);
 void rg_ctx_destroy(rg_ctx *ctx);
 
-/* Bytes of device scratch a grow of this size needs (worst case, so no call can overflow). */
+/* Bytes of device scratch a grow of this size needs: the worst case, so that no call can overflow, up to ~17 Gvoxel;
+ * beyond that the node space is sized for an average of 2048 nodes per tile (the worst case would not fit 32-bit node
+ * ids) and an input that needs more is refused through the status word (rg_ctx_status fails with "out of node ids"). */
 int64_t rg_workspace_bytes(int64_t nx, int64_t ny, int64_t nz, int nseeds);
 
 /* Pre-size the context's scratch so that later calls do not allocate. */

@@ -395,7 +395,14 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
 {
     int64_t ntx = (nx + C::TX - 1) / C::TX, nty = (ny + C::TY - 1) / C::TY, ntz = (nz + C::TZ - 1) / C::TZ;
     int64_t ntiles = ntx * nty * ntz;
-    int64_t node_cap = 1 + ntiles * ((int64_t)C::ENT_MAX + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
+    /* Node ids: one fixed block per tile for the fast pass, then room for the full pass.  The worst case (every tile
+       through the full pass with a node per face entry) stops fitting 32 bits at ~17 Gvoxel, long before a 180 GB card
+       is full; beyond that -- or when RG_NODE_BUDGET says so -- the full pass gets an average of RG_NODE_BUDGET (2048)
+       nodes per tile.  Running out is detected on the device (status bit 1, rg_ctx_status fails), never silent. */
+    int64_t budget = (int64_t)C::ENT_MAX;
+    { const char *e = getenv("RG_NODE_BUDGET"); if (e && atoll(e) > 0 && atoll(e) < budget) budget = atoll(e); }
+    int64_t node_cap = 1 + ntiles * (budget + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
+    if (node_cap >= (1ll << 32)) node_cap = 1 + ntiles * ((budget < 2048 ? budget : 2048) + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
     if (ntiles >= (1ll << 31) || node_cap >= (1ll << 32)) return fail(RG_ERR_TOO_LARGE, "volume too large for 32-bit node ids");
     L.ntx = (int)ntx; L.nty = (int)nty; L.ntz = (int)ntz; L.ntiles = (uint32_t)ntiles; L.node_cap = (uint32_t)node_cap;
     size_t o = 0;
@@ -757,7 +764,11 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
     CK(cudaStreamSynchronize(c->last_stream));
     if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX]; stats[3] = c->h_status[CTR_NFLAGGED]; }
     if (c->h_status[CTR_STATUS]) {
-        snprintf(g_err, sizeof g_err, "engine self-check failed: status=0x%x mismatching faces=%u", c->h_status[CTR_STATUS], c->h_status[CTR_FACE_MISMATCH]);
+        if (c->h_status[CTR_STATUS] & ST_NODE_OVERFLOW)
+            snprintf(g_err, sizeof g_err, "out of node ids (status=0x%x): this input needs more nodes per tile than the workspace holds "
+                     "(volumes beyond ~17 Gvoxel and RG_NODE_BUDGET runs size it for an average, not the worst case)", c->h_status[CTR_STATUS]);
+        else
+            snprintf(g_err, sizeof g_err, "engine self-check failed: status=0x%x mismatching faces=%u", c->h_status[CTR_STATUS], c->h_status[CTR_FACE_MISMATCH]);
         return RG_ERR_INTERNAL;
     }
     return RG_OK;

@@ -212,10 +212,13 @@ def test_c2_full_size_properties(rg, ctx, oracle):
 
 
 # ---------------------------------------------------------------- z-slab path on one device ("fake cluster")
-def slab_grow_one_device(rg, img, seeds, T, G):
-    """run the multi-rank protocol for G logical ranks on one GPU by calling the C ABI phases in turn"""
+def slab_grow_one_device(rg, img, seeds, T, G, return_parts=False):
+    """run the multi-rank protocol for G logical ranks on one GPU by calling the C ABI phases in turn.
+    img: numpy array, or a CUDA tensor (then nothing passes through the host; use return_parts=True to get the
+    per-rank mask tensors instead of one assembled array)"""
     import torch
     lib = rg.load_library()
+    on_device = hasattr(img, "is_cuda")
     rows = img.ndim == 2                                            # an image is cut into row slabs, a volume into z-slabs
     nz, ny, nx = ((1,) + img.shape) if rows else img.shape
     plane = nx if rows else nx * ny
@@ -226,7 +229,7 @@ def slab_grow_one_device(rg, img, seeds, T, G):
         h = ctypes.c_void_p(); assert lib.rg_ctx_create(0, ctypes.byref(h)) == 0
         buf = torch.zeros((z1 - z0 + 2) * plane, dtype=torch.uint8, device="cuda")
         lo, hi = max(z0 - 1, 0), min(z1 + 1, ny if rows else nz)
-        buf[(lo - z0 + 1) * plane:(hi - z0 + 1) * plane] = torch.from_numpy(img[lo:hi].reshape(-1)).cuda()
+        buf[(lo - z0 + 1) * plane:(hi - z0 + 1) * plane] = img[lo:hi].reshape(-1) if on_device else torch.from_numpy(img[lo:hi].reshape(-1)).cuda()
         mask = torch.empty((z1 - z0) * plane, dtype=torch.uint8, device="cuda")
         s = np.asarray(seeds, np.int32).reshape(-1, 3)
         s = s[(s[:, axis] >= z0) & (s[:, axis] < z1)].copy()
@@ -264,12 +267,13 @@ def slab_grow_one_device(rg, img, seeds, T, G):
                 assert lib.rg_slab_resolve_apply(h, xpar.data_ptr(), ranks[me]["lists"][side].data_ptr(), int(cnt[me, side]), int(off[me]), None) == 0
         assert lib.rg_slab_finish(h, None) == 0
         torch.cuda.synchronize()
-    out = np.concatenate([rk["mask"].cpu().numpy() for rk in ranks]).reshape(img.shape)
     for rk in ranks:
         st = (ctypes.c_uint32 * 4)()
         assert lib.rg_ctx_status(rk["h"], st) == 0
         lib.rg_ctx_destroy(rk["h"])
-    return out
+    if return_parts:
+        return [(rk["z0"], rk["z1"], rk["mask"]) for rk in ranks]
+    return np.concatenate([rk["mask"].cpu().numpy() for rk in ranks]).reshape(tuple(img.shape))
 
 
 @pytest.mark.parametrize("G", [2, 4, 8])
@@ -285,6 +289,60 @@ def test_slabs_random_ragged(rg, ctx, oracle, G):
     img = rng.integers(0, 3, size=(37, 45, 150), dtype=np.uint8)
     seeds = np.stack([rng.integers(0, 150, 6), rng.integers(0, 45, 6), rng.integers(0, 37, 6)], 1)
     assert (slab_grow_one_device(rg, img, seeds, 1, G) == oracle.grow(img, seeds, 1)).all()
+
+
+def test_node_budget_overflow_is_reported(rg, oracle, monkeypatch):
+    """volumes beyond ~17 Gvoxel (and RG_NODE_BUDGET runs) size the node space for an average number of nodes per
+    tile; an input that needs more must fail loudly through the status word, and succeed again with room"""
+    import torch
+    img, seeds, T = oracle.synth("c3", 128)                      # every tile goes through the full pass with hundreds of nodes
+    want = oracle.grow(img, seeds, T)
+    d_img = torch.from_numpy(img).cuda(); d_seeds = torch.from_numpy(seeds).cuda(); out = torch.empty_like(d_img)
+    monkeypatch.setenv("RG_NODE_BUDGET", "4")
+    c1 = rg.Context(0)
+    c1.grow(d_img, d_seeds, T, out)
+    torch.cuda.synchronize()
+    st = (ctypes.c_uint32 * 4)()
+    assert c1.lib.rg_ctx_status(c1.handle, st) != 0 and (st[1] & 1)
+    assert b"node ids" in c1.lib.rg_last_error()
+    monkeypatch.delenv("RG_NODE_BUDGET")
+    c2 = rg.Context(0)
+    c2.grow(d_img, d_seeds, T, out)
+    torch.cuda.synchronize()
+    assert c2.status()["status"] == 0 and (out.cpu().numpy() == want).all()
+
+
+def test_volume_beyond_the_worst_case_node_space(rg, oracle):
+    """2048 x 2048 x 4608 (19.3 Gvoxel, 2.25 x the benchmark volume): the worst-case node count no longer fits 32 bits,
+    so the workspace is sized by budget.  Checked against the same volume grown as three z-slabs (each small enough for
+    worst-case sizing) joined by the interface exchange -- a different code path over the same data."""
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    if free < 150e9:
+        pytest.skip("needs ~135 GB of device memory")
+    n, nz = 2048, 4608
+    lib = rg.load_library()
+    ctx = rg.Context(0)
+    img = torch.empty((nz, n, n), dtype=torch.uint8, device="cuda")
+    for z0 in range(0, nz, n):                                     # copies of the C4 cube stacked along z
+        z1 = min(z0 + n, nz)
+        ctx.synth(4, img[z0:z1], n, 0x5EED0004, z_begin=0, z_end=z1 - z0)
+    base = rg.synth_seeds(4, n, 0x5EED0004)
+    seeds = np.concatenate([base + [0, 0, k * n] for k in range(3)]).astype(np.int32)
+    seeds = seeds[seeds[:, 2] < nz]
+    d_seeds = torch.from_numpy(np.ascontiguousarray(seeds)).cuda()
+    assert lib.rg_workspace_bytes(n, n, nz, len(seeds)) < 2.5 * n * n * nz      # budgeted, not 2 B/voxel + the worst-case nodes
+    out = torch.empty_like(img)
+    ctx.grow(img, d_seeds, 1, out)
+    torch.cuda.synchronize()
+    st = ctx.status()
+    assert st["status"] == 0, st
+    region = sum(int(torch.count_nonzero(out[z:z + 256])) for z in range(0, nz, 256))     # no full-size temporaries
+    assert region > 2 * 572079655                                    # at least the solids of two whole copies
+    ctx.close()
+    torch.cuda.empty_cache()
+    for z0, z1, m in slab_grow_one_device(rg, img, seeds, 1, 3, return_parts=True):
+        assert torch.equal(m.view(z1 - z0, n, n), out[z0:z1]), (z0, z1)
 
 
 @pytest.mark.parametrize("G", [2, 3, 8])
