@@ -118,6 +118,81 @@ def test_seed_edge_cases(rg, ctx, oracle):
     assert wall.sum() == 20 * 40 and wall[:, :, 48].all()
 
 
+@pytest.mark.parametrize("shape", [(24, 48, 128), (300, 272)])
+@pytest.mark.parametrize("off_img,off_mask", [(1, 0), (0, 3), (5, 9), (16, 32)])
+def test_misaligned_device_pointers(rg, ctx, oracle, shape, off_img, off_mask):
+    """rows that are a multiple of 16 bytes but buffers that do not start on a 16-byte boundary (a view into a larger
+    allocation): the engine must leave its vector / TMA paths on its own"""
+    import torch
+    rng = np.random.default_rng(off_img * 100 + off_mask + len(shape))
+    img = rng.integers(0, 3, size=shape, dtype=np.uint8)
+    nvox = img.size
+    dims = shape[::-1] if len(shape) == 3 else (shape[1], shape[0], 1)
+    seeds = np.stack([rng.integers(0, d, 6) for d in dims], 1).astype(np.int32)
+    big_i = torch.zeros(nvox + 64, dtype=torch.uint8, device="cuda")
+    big_m = torch.full((nvox + 64,), 7, dtype=torch.uint8, device="cuda")
+    d_img = big_i[off_img:off_img + nvox].view(*shape); d_img.copy_(torch.from_numpy(img))
+    d_out = big_m[off_mask:off_mask + nvox].view(*shape)
+    assert d_img.data_ptr() % 16 == off_img % 16 and d_out.data_ptr() % 16 == off_mask % 16
+    ctx.grow(d_img, torch.from_numpy(seeds).cuda(), 1, d_out)
+    torch.cuda.synchronize()
+    assert ctx.status()["status"] == 0
+    assert (d_out.cpu().numpy() == oracle.grow(img, seeds, 1)).all()
+    assert bool((big_m[:off_mask] == 7).all()) and bool((big_m[off_mask + nvox:] == 7).all())      # nothing written outside the mask
+
+
+def test_one_context_many_shapes_and_a_side_stream(rg, oracle):
+    """a context is reused across sizes (its scratch grows), dimensionalities and streams"""
+    import torch
+    c = rg.Context(0)
+    side = torch.cuda.Stream()
+    rng = np.random.default_rng(77)
+    for shape in [(8, 16, 64), (200, 144), (40, 70, 130), (1, 1, 1), (64, 64), (33, 65, 200), (17, 40, 96)]:
+        img = rng.integers(0, 3, size=shape, dtype=np.uint8)
+        dims = shape[::-1] if len(shape) == 3 else (shape[1], shape[0], 1)
+        seeds = np.stack([rng.integers(0, d, 4) for d in dims], 1).astype(np.int32)
+        d_img = torch.from_numpy(img).cuda(); d_seeds = torch.from_numpy(seeds).cuda(); out = torch.full_like(d_img, 9)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            c.grow(d_img, d_seeds, 1, out)                          # rgb200 launches on torch's current stream
+        side.synchronize()
+        assert c.status()["status"] == 0
+        assert (out.cpu().numpy() == oracle.grow(img, seeds, 1)).all(), shape
+    c.close()
+
+
+def test_seed_set_algebra_at_benchmark_scale(rg, ctx):
+    """properties that need no oracle (C4 geometry at 1024^3, 1 Gvoxel): the region of a union of seed sets is the union
+    of the regions; every in-range seed is in its region; growing again from a voxel of a region component returns
+    that component; a second call on the same inputs returns the same bytes"""
+    import torch
+    n = 1024
+    img = torch.empty((n, n, n), dtype=torch.uint8, device="cuda")
+    ctx.synth(4, img, n, 0x5EED0004)
+    seeds = rg.synth_seeds(4, n, 0x5EED0004)
+    d_all = torch.from_numpy(seeds).cuda()
+    a, b = seeds[:5].copy(), seeds[5:].copy()
+    m_all = torch.empty_like(img); m_a = torch.empty_like(img); m_b = torch.empty_like(img); again = torch.empty_like(img)
+    ctx.grow(img, d_all, 1, m_all)
+    ctx.grow(img, torch.from_numpy(a).cuda(), 1, m_a)
+    ctx.grow(img, torch.from_numpy(b).cuda(), 1, m_b)
+    ctx.grow(img, d_all, 1, again)
+    torch.cuda.synchronize()
+    assert ctx.status()["status"] == 0
+    assert torch.equal(m_all, m_a | m_b) and torch.equal(m_all, again)
+    assert bool((m_all[d_all[:, 2].long(), d_all[:, 1].long(), d_all[:, 0].long()] == 1).all())
+    # the component of the first seed (the big sphere), regrown from some other voxel of it
+    ctx.grow(img, torch.from_numpy(seeds[:1].copy()).cuda(), 1, m_a)
+    torch.cuda.synchronize()
+    nz = torch.nonzero(m_a[n // 5])                                  # a plane that cuts the sphere
+    assert len(nz) > 1000
+    y, x = [int(v) for v in nz[len(nz) // 2]]
+    other = torch.tensor([[x, y, n // 5]], dtype=torch.int32, device="cuda")
+    ctx.grow(img, other, 1, m_b)
+    torch.cuda.synchronize()
+    assert torch.equal(m_a, m_b)
+
+
 def test_many_seeds_radix_sort_path(rg, ctx, oracle):
     rng = np.random.default_rng(3)
     img = rng.integers(0, 4, size=(40, 70, 130), dtype=np.uint8)
