@@ -16,12 +16,13 @@
  *   pass B  (merge_faces)   union-find over the coarse node graph with lock-free hooking; seeds
  *           are pre-hooked to node 0, so "in the region" == "root is node 0".  One launch, no
  *           global iteration and no host round trip, whatever the region's diameter.
- *   pass C  (tile_pass_c)   tiles with no selected node are zero-filled without reading the
- *           image; the others recompute their local components and write 0/1 mask bytes with
- *           16-byte stores.  Writes 1 B/voxel, reads <= 1 B/voxel.
+ *   pass C  (tile_pass_c)   tiles with no selected node need no image read (their mask bytes are
+ *           zeros); the others re-stage, rebuild the link planes and flood the region from the selected
+ *           representatives with bit-parallel sweeps (stride planes carry it 1, 2, 4, ... rows and planes
+ *           per sweep), then write 0/1 mask bytes with 16-byte stores.  Writes 1 B/voxel, reads <= 1 B/voxel.
  *
  * Every body is written against an `Exec` (thread id, parallel-for, barrier, scan) so that the
- * same source runs as a CUDA block (rg_kernels.cu) and, for the CPU logic tests only, as a
+ * same source runs as a CUDA block (rg_engine.cu) and, for the CPU logic tests only, as a
  * sequential loop (tests/emu).  See rg_port.h.
  */
 #pragma once
