@@ -34,9 +34,11 @@ enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
 enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_WORDS = 8 };
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
-template <int TX_, int TY_, int TZ_>
+/* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
+   the lean layout of the fast labelling pass, which fetches that one column by itself and gains a fourth CTA per SM. */
+template <int TX_, int TY_, int TZ_, int XR_ = 16>
 struct TileCfg {
-    static constexpr int TX = TX_, TY = TY_, TZ = TZ_;
+    static constexpr int TX = TX_, TY = TY_, TZ = TZ_, XR = XR_;
     static constexpr int WX = TX / 32;             /* 32-voxel words per row */
     static constexpr int NW = WX * TY * TZ;        /* words per tile */
     static constexpr int NV = TX * TY * TZ;        /* voxels per tile */
@@ -44,7 +46,8 @@ struct TileCfg {
     static constexpr int PZ = TZ + 2 * HZ, PY = TY + 2;
     static constexpr int CX = TX / 16;             /* 16-byte chunks per row (own voxels) */
     static constexpr int XO = 16;                  /* staged rows start 16 bytes left of the tile: x = -1 is byte 15 */
-    static constexpr int RS = TX + 32;             /* staged row stride: [x0-16, x0+TX+16) */
+    static constexpr int RS = TX + XO + XR;        /* staged row stride: [x0-16, x0+TX+XR) */
+    static_assert(XR == 0 || XR == 16, "the right margin is one 16-byte chunk or nothing");
     static constexpr int CXH = RS / 16;            /* 16-byte chunks per staged row */
     static constexpr int PS = PY * RS;             /* staged plane stride */
     static constexpr int IMG_BYTES = PZ * PS;
@@ -77,6 +80,9 @@ typedef TileCfg<RG_TX3, RG_TY3, RG_TZ3> Cfg3D;
 #define RG_TY2 126
 #endif
 typedef TileCfg<128, RG_TY2, 1> Cfg2D;
+/* the staging layout the fast labelling pass uses for a tile shape: lean for volumes, unchanged for images (their
+   staged tile is 20 KB anyway) */
+template <class C> struct LeanOf { typedef TileCfg<C::TX, C::TY, C::TZ, C::HZ ? 0 : C::XR> type; };
 
 struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint32_t node_base;          /* first global node id of this tile */
@@ -155,7 +161,7 @@ struct alignas(128) TileSmem {
     uint32_t scal[16];
     uint32_t scan_scratch[40];
 };
-enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8, SC_NSLOW = 9 };
+enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8, SC_NSLOW = 9, SC_CNT0 = 16 };
 
 /* ---------------------------------------------------------------- small helpers */
 RG_FN uint32_t valid_bits(int64_t n) { return n >= 32 ? 0xFFFFFFFFu : n <= 0 ? 0u : ((1u << n) - 1u); }
@@ -279,7 +285,7 @@ RG_FN void load_tile(Exec &ex, const Params &P, uint8_t *img, int64_t x0, int64_
         int c = it % C::CXH, r = it / C::CXH;
         int py = r % C::PY, pz = r / C::PY;
         int ly = py - 1, lz = pz - C::HZ;
-        bool yh = (ly < 0 || ly >= C::TY), zh = (lz < 0 || lz >= C::TZ), xh = (c == 0 || c == C::CXH - 1);
+        bool yh = (ly < 0 || ly >= C::TY), zh = (lz < 0 || lz >= C::TZ), xh = (c == 0 || (C::XR > 0 && c == C::CXH - 1));
         bool want = !(yh && zh) && !(xh && (yh || zh)) && (halo || !(yh || zh || xh));
         if (!want) return;                                      /* never read: edge / corner columns, halo of pass C */
         int64_t gx = x0 - C::XO + 16 * c, gy = y0 + ly, gz = z0 + lz;

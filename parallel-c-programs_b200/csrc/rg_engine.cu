@@ -135,30 +135,31 @@ struct DevExec {
 /* ------------------------------------------------------------------ kernels */
 #define RG_THREADS 512          /* full tile passes: 2 CTAs/SM (105 KB smem each) */
 #ifndef RG_FAST_THREADS
-#define RG_FAST_THREADS 384     /* fast labelling pass: 3 CTAs/SM (68 KB smem each) */
+#define RG_FAST_THREADS 256     /* fast labelling pass: 4 CTAs/SM (56 KB smem each, lean staging layout) */
 #endif
 #ifndef RG_FAST_MINB
-#define RG_FAST_MINB 3
+#define RG_FAST_MINB 4
 #endif
 #define RG_FLAG_THREADS 256     /* flag / zero-fill: no smem, 8 tiles per CTA */
 #define RG_PERSISTENT_CTAS (148 * 2)
 
-/* pass A, fast path: every tile */
+/* pass A, fast path: every tile.  C = the tile shape; the kernel stages it in the lean layout (LeanOf<C>) */
 template <class C>
 __global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
+    typedef typename LeanOf<C>::type L;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    FastSmem<C> &s = *reinterpret_cast<FastSmem<C> *>(smem_raw);
+    FastSmem<L> &s = *reinterpret_cast<FastSmem<L> *>(smem_raw);
     DevExec<RG_FAST_THREADS> ex; ex.tmap = &tmap;
     ex.grid3d = gridDim.y * gridDim.z > 1 || (P.nty == 1 && P.ntz == 1);
     if (P.use_tma) ex.mbar_init(&s.mbar);
     const uint32_t tile = ex.grid3d ? (blockIdx.z * (uint32_t)P.nty + blockIdx.y) * (uint32_t)P.ntx + blockIdx.x : blockIdx.x;
-    tile_pass_a_fast<C>(ex, P, tile, s);
+    tile_pass_a_fast<L>(ex, P, tile, s);
 }
 
 static_assert(sizeof(TileSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2 && sizeof(FloodSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2,
               "the persistent passes are sized for two CTAs per SM");
-static_assert(3 * (sizeof(FastSmem<Cfg3D>) + 1024) <= 227 * 1024, "the fast labelling pass is sized for three CTAs per SM");
+static_assert(RG_FAST_MINB * (sizeof(FastSmem<LeanOf<Cfg3D>::type>) + 1024) <= 228 * 1024, "the fast labelling pass is sized for RG_FAST_MINB CTAs per SM");
 
 /* pass A, full path: the tiles the fast path listed (persistent CTAs) */
 #ifdef RG_PARENT32
@@ -347,6 +348,7 @@ struct rg_ctx {
     ResolveArgs *d_rargs;                      /* device copy of the exchange bookkeeping (optimistic exchange) */
     dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
+    CUtensorMap last_tmap_fast;                /* the same image with the lean box of the fast labelling pass */
     bool profile; cudaEvent_t ev[7]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
 };
 
@@ -491,7 +493,7 @@ extern "C" int rg_ctx_reserve(rg_ctx *c, int64_t nx, int64_t ny, int64_t nz, int
 template <class C>
 static int set_attrs()
 {
-    CK(cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<typename LeanOf<C>::type>)));
     CK(cudaFuncSetAttribute(k_pass_a_full<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
     CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FloodSmem<C>)));
     return RG_OK;
@@ -525,7 +527,8 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     /* the tensor map covers the neighbours' halo planes (volumes) or halo rows (images) as well */
     const int64_t ey = ext_ylo<C>(P) + ext_yhi<C>(P), ez = ext_zlo<C>(P) + ext_zhi<C>(P);
     const uint8_t *map_base = d_image - (size_t)ext_zlo<C>(P) * nx * ny - (size_t)ext_ylo<C>(P) * nx;
-    P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, map_base, nx, ny + ey, nz + ez)) ? 1 : 0;
+    P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, map_base, nx, ny + ey, nz + ez)
+                 && make_tmap<typename LeanOf<C>::type>(&c->last_tmap_fast, map_base, nx, ny + ey, nz + ez)) ? 1 : 0;
     P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
     P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
     P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
@@ -548,7 +551,12 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     const bool g3 = L.nty <= 65535 && L.ntz <= 65535;
     const dim3 tile_grid = g3 ? dim3((unsigned)L.ntx, (unsigned)L.nty, (unsigned)L.ntz) : dim3(L.ntiles, 1, 1);
     c->last_grid = tile_grid;
-    k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<C>), st>>>(P, c->last_tmap);
+    {
+        static int pad = -1;                                        /* tuning: RG_FAST_PAD_SMEM=bytes lowers the CTAs per SM */
+        if (pad < 0) { const char *e = getenv("RG_FAST_PAD_SMEM"); pad = e ? atoi(e) : 0;
+                       if (pad) cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<typename LeanOf<C>::type>) + pad); }
+        k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<typename LeanOf<C>::type>) + pad, st>>>(P, c->last_tmap_fast);
+    }
     if (c->profile) cudaEventRecord(c->ev[2], st);
     if (!P.debug_stop || P.debug_stop >= 10) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);
     if (c->profile) cudaEventRecord(c->ev[3], st);

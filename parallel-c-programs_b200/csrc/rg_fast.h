@@ -39,27 +39,31 @@ template <class C>
 struct alignas(128) FastSmem {
     uint8_t img[C::IMG_BYTES];
     uint64_t mbar;
-    uint32_t fmask[C::FW_TOTAL];
-    uint16_t fprefix[C::FW_TOTAL + 2];
+    /* the cross-tile edge words and their prefix sums are dead once the edge list exists; the list of the longer
+       walks, written after that, takes their place */
+    union {
+        struct { uint32_t fmask[C::FW_TOTAL]; uint16_t fprefix[C::FW_TOTAL + 2]; } f;
+        uint16_t slow[FAST_ENT_MAX];              /* edges whose start voxel has a similar neighbour inside the tile */
+    } u;
     uint16_t ent_root[FAST_ENT_MAX];              /* per edge: start voxel, later the hash slot of its component */
-    uint16_t slow[FAST_ENT_MAX];                  /* edges whose start voxel has a similar neighbour inside the tile */
-    alignas(16) uint32_t tab[HASH_N];             /* open addressing: representative + 1, 0 = empty */
+    alignas(16) uint16_t tab[HASH_N];             /* open addressing: representative + 1 (<= 32768), 0 = empty */
     uint16_t slotid[HASH_N];                      /* dense node id of each occupied slot (scan after the walks) */
     alignas(16) uint32_t seedtab[HASH_N / 32];    /* bit per slot: the component holds a seed */
-    uint32_t scal[16];
+    uint8_t xr[C::XR ? 16 : C::TY * C::TZ];       /* lean layout: the x = TX halo column, one byte per (y, z) */
+    uint32_t scal[24];                            /* SC_* and, from SC_CNT0 on, the six face-list lengths */
     uint32_t scan_scratch[40];
-    static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit");
+    static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit; hash keys are 16 bits");
 };
 
 /* find or insert representative `root`; returns its slot.  Dense node ids are handed out afterwards by one
    scan over the slots (a shared counter bumped by every inserting thread serialises the whole phase). */
-RG_FN uint32_t hash_slot(uint32_t *tab, uint32_t *scal, uint32_t root)
+RG_FN uint32_t hash_slot(uint16_t *tab, uint32_t *scal, uint32_t root)
 {
     const uint32_t key = root + 1u;
     uint32_t slot = (root * 2654435761u) >> (32 - HASH_BITS);
     for (int probe = 0; probe < HASH_N; probe++) {
-        uint32_t cur = ldv32(&tab[slot]);
-        if (cur == 0u) cur = cas32(&tab[slot], 0u, key);
+        uint32_t cur = ldv16(&tab[slot]);
+        if (cur == 0u) cur = cas16(&tab[slot], (uint16_t)0, (uint16_t)key);
         if (cur == 0u || cur == key) return slot;
         slot = (slot + 1u) & (HASH_N - 1);
     }
@@ -150,7 +154,7 @@ RG_FN uint32_t face_voxel(int f, int idx, int b, int vy, int vz)
 /* cross-tile edge masks of the six faces, from the staged bytes (the same words build_edges<FACES>
  * produces, without touching the interior) */
 template <class C, class Exec>
-RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint32_t *fmask, int64_t x0, int64_t y0, int64_t z0)
+RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const uint8_t *xr, uint32_t *fmask, int64_t x0, int64_t y0, int64_t z0)
 {
     const int64_t nx = P.nx, ny = P.ny, nz = P.nz;
     const int tmode = P.tmode; const uint32_t t4 = P.t4;
@@ -191,7 +195,7 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, uint3
         const int y = q % C::TY, z = q / C::TY;
         if ((side ? !has_xp : !has_xm) || y >= vy || z >= vz) return;
         const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
-        const uint32_t own = o[0], other = o[side ? 1 : -1];
+        const uint32_t own = o[0], other = side ? (C::XR ? o[1] : xr[q]) : o[-1];       /* lean layout: the x = TX column is in xr */
         if (absdiff(own, other) < P.thr) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
     });
 }
@@ -227,8 +231,17 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
 
     if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
     if (P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);          /* fire-and-forget stores: they fill the load's latency */
-    ex.pfor(C::FW_TOTAL, [&](int i) { s.fmask[i] = 0; });
-    ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
+    ex.pfor(C::FW_TOTAL, [&](int i) { s.u.f.fmask[i] = 0; });
+    ex.pfor(HASH_N / 8, [&](int i) { st128(&s.tab[8 * i], u32x4{0, 0, 0, 0}); });
+    if (!C::XR) {
+        /* lean layout: the x = TX column is not in the staged box; one byte per (y, z) straight from the image (the
+           neighbouring tile's CTA reads the same lines, so these come from L2) */
+        const bool has_col = x0 + C::TX < P.nx;
+        ex.pfor(C::TY * C::TZ, [&](int q) {
+            const int y = q % C::TY, z = q / C::TY;
+            s.xr[q] = (has_col && y < vy && z < vz) ? P.image[((z0 + z) * P.ny + (y0 + y)) * P.nx + x0 + C::TX] : (uint8_t)0;
+        });
+    }
     ex.pfor(HASH_N / 32, [&](int i) { s.seedtab[i] = 0; });
     if (ex.tid() == 0) {
         uint32_t lo, hi; seed_range(P, tile, lo, hi);
@@ -254,11 +267,14 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             uniform = !ex.sync_or(differs);
         }
     }
-    build_face_masks<C>(ex, P, s.img, s.fmask, x0, y0, z0);
+    build_face_masks<C>(ex, P, s.img, s.xr, s.u.f.fmask, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 3) return;
-    const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.fmask[i]); }, s.fprefix, s.scan_scratch);
-    if (ex.tid() == 0) s.fprefix[C::FW_TOTAL] = (uint16_t)etot;
+    const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.u.f.fmask[i]); }, s.u.f.fprefix, s.scan_scratch);
+    if (ex.tid() == 0) {
+        s.u.f.fprefix[C::FW_TOTAL] = (uint16_t)etot;
+        for (int f = 0; f < 6; f++) s.scal[SC_CNT0 + f] = (uint32_t)(s.u.f.fprefix[C::fw_off(f + 1)] - s.u.f.fprefix[C::fw_off(f)]);   /* the prefix sums do not live to the end */
+    }
     const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
     const uint32_t base = fast_node_base(tile);
     uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
@@ -271,11 +287,11 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         if (etot > (uint32_t)FAST_ENT_MAX) { fast_give_up<C>(ex, P, tile); return; }     /* same total in every thread */
         /* start voxel of every cross-tile edge, in list order ... */
         ex.pfor(C::FW_TOTAL, [&](int fw) {
-            uint32_t m = s.fmask[fw];
+            uint32_t m = s.u.f.fmask[fw];
             if (!m) return;
             int f = 0; while (fw >= C::fw_off(f + 1)) f++;
             const int idx = fw - C::fw_off(f);
-            uint32_t slot = s.fprefix[fw];
+            uint32_t slot = s.u.f.fprefix[fw];
             while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vy, vz); }
         });
         ex.sync();
@@ -283,7 +299,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
            own component; the others go to a compact list so that the longer walks fill whole warps. */
         ex.pfor((int)etot, [&](int e) {
             const uint32_t v = s.ent_root[e];
-            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
+            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
             else s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, v);
         });
         {
@@ -299,7 +315,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         ex.sync();
         if (P.debug_stop == 6) return;
         ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
-            const int e = s.slow[i];
+            const int e = s.u.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
             const uint32_t nb0 = neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v);
@@ -326,7 +342,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     if (ex.tid() == 0) {
         TileRec rc;
         rc.node_base = base; rc.nnodes = nnodes;
-        for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]);
+        for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)s.scal[SC_CNT0 + f];
         rc.uniform = uniform ? 1 : 0; rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
         P.rec[tile] = rc;
     }

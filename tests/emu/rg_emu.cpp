@@ -91,9 +91,10 @@ template <class C> static void emu_label(EmuState &E)
     HostExec ex; const Params &P = E.P;
     uint32_t ntiles = (uint32_t)P.ntx * P.nty * P.ntz;
     TileSmem<C> *s = (TileSmem<C> *)aligned_alloc(128, (sizeof(TileSmem<C>) + 127) / 128 * 128);
-    FastSmem<C> *f = (FastSmem<C> *)aligned_alloc(128, (sizeof(FastSmem<C>) + 127) / 128 * 128);
+    typedef typename LeanOf<C>::type LC;                             /* the fast pass stages in the lean layout, as the kernel does */
+    FastSmem<LC> *f = (FastSmem<LC> *)aligned_alloc(128, (sizeof(FastSmem<LC>) + 127) / 128 * 128);
     if (g_force_full) { for (uint32_t t = 0; t < ntiles; t++) E.clist[t] = t; E.counters[CTR_NCOMPLEX] = ntiles; }
-    else for (uint32_t t = 0; t < ntiles; t++) { memset(f, 0xA5, sizeof *f); tile_pass_a_fast<C>(ex, P, t, *f); }
+    else for (uint32_t t = 0; t < ntiles; t++) { memset(f, 0xA5, sizeof *f); tile_pass_a_fast<LC>(ex, P, t, *f); }
     memset(s, 0xA5, sizeof *s);
     pass_a_full_list<C>(ex, P, *s);
     merge_faces<C>(ex, P);
