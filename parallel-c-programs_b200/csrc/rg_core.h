@@ -704,13 +704,15 @@ RG_FN void zero_tile(Exec &ex, const Params &P, int64_t x0, int64_t y0, int64_t 
 /* shared memory of pass C: staged tile, edge planes, region bits */
 template <class C>
 struct alignas(128) FloodSmem {
-    uint8_t img[C::IMG_BYTES];
+    union alignas(128) U {
+        uint8_t img[C::IMG_BYTES];                 /* staged tile: dead once the link planes exist */
+        StridePlanes<C> sp;                        /* built (if at all) after the first unit-stride sweeps */
+    } u;
     uint64_t mbar;
     alignas(16) uint32_t ex[C::NW];
     alignas(16) uint32_t ey[C::NW];
     alignas(16) uint32_t ez[C::NW];
     alignas(16) uint32_t M[C::NW];                 /* bit i: voxel i is in the region */
-    StridePlanes<C> sp;
     uint32_t scal[16];
 };
 
@@ -726,8 +728,8 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     const TileRec rc = P.rec[tile];
 
     if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
-    const bool tma = ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0);
-    if (!tma) load_tile<C>(ex, P, s.img, x0, y0, z0, false);
+    const bool tma = ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0);
+    if (!tma) load_tile<C>(ex, P, s.u.img, x0, y0, z0, false);
     ex.pfor(C::NW / 4, [&](int i) { st128(&s.M[4 * i], u32x4{0, 0, 0, 0}); });
     if (ex.tid() == 0) s.scal[SC_ANY] = 0;
     ex.sync();
@@ -743,17 +745,17 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     ex.sync();
     if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
     if (P.debug_stop == 20) return;
-    build_edges<C, false>(ex, P, s.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
+    build_edges<C, false>(ex, P, s.u.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 21) return;
     /* A region advances a whole run per sweep in x but one row / plane per sweep in y and z, so a tile that is still
        changing after a few sweeps (a solid: up to TY + TZ of them) gets stride planes and continues 1, 2, 4, ...
        rows and planes at a time. */
     bool more = true;
-    for (int i = 0; i < FLOOD_PLAIN_SWEEPS && more; i++) more = flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.sp, false);
+    for (int i = 0; i < FLOOD_PLAIN_SWEEPS && more; i++) more = flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.u.sp, false);
     if (more) {
-        build_stride_planes<C>(ex, s.ey, s.ez, s.sp);
-        while (flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.sp, true)) { }
+        build_stride_planes<C>(ex, s.ey, s.ez, s.u.sp);
+        while (flood_sweep<C>(ex, s.M, s.ex, s.ey, s.ez, s.u.sp, true)) { }
     }
     if (P.debug_stop == 22) return;
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {

@@ -142,6 +142,8 @@ struct DevExec {
 #endif
 #define RG_FLAG_THREADS 256     /* flag / zero-fill: no smem, 8 tiles per CTA */
 #define RG_PERSISTENT_CTAS (148 * 2)
+#define RG_PASSC_THREADS 384    /* pass C: 3 CTAs/SM (66 KB smem each) */
+#define RG_PASSC_CTAS (148 * 3)
 
 /* pass A, fast path: every tile.  C = the tile shape; the kernel stages it in the lean layout (LeanOf<C>) */
 template <class C>
@@ -157,8 +159,8 @@ __global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(c
     tile_pass_a_fast<L>(ex, P, tile, s);
 }
 
-static_assert(sizeof(TileSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2 && sizeof(FloodSmem<Cfg3D>) + 1024 <= 227 * 1024 / 2,
-              "the persistent passes are sized for two CTAs per SM");
+static_assert(sizeof(TileSmem<Cfg3D>) + 1024 <= 228 * 1024 / 2, "the full labelling pass is sized for two CTAs per SM");
+static_assert(3 * (sizeof(FloodSmem<LeanOf<Cfg3D>::type>) + 1024) <= 228 * 1024, "pass C is sized for three CTAs per SM");
 static_assert(RG_FAST_MINB * (sizeof(FastSmem<LeanOf<Cfg3D>::type>) + 1024) <= 228 * 1024, "the fast labelling pass is sized for RG_FAST_MINB CTAs per SM");
 
 /* pass A, full path: the tiles the fast path listed (persistent CTAs) */
@@ -185,15 +187,17 @@ __global__ void __launch_bounds__(RG_FLAG_THREADS) k_flag_tiles(const Params P)
     flag_tiles_all<C>(ex, P);
 }
 
-/* pass C, part 2: the listed tiles (persistent CTAs) */
+/* pass C, part 2: the listed tiles (persistent CTAs, 3 per SM: the tile is staged in the lean layout and the
+   stride planes of the flood reuse its bytes) */
 template <class C>
-__global__ void __launch_bounds__(RG_THREADS, 2) k_pass_c(const Params P, const __grid_constant__ CUtensorMap tmap)
+__global__ void __launch_bounds__(RG_PASSC_THREADS, 3) k_pass_c(const Params P, const __grid_constant__ CUtensorMap tmap)
 {
+    typedef typename LeanOf<C>::type L;
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    FloodSmem<C> &s = *reinterpret_cast<FloodSmem<C> *>(smem_raw);
-    DevExec<RG_THREADS> ex; ex.tmap = &tmap;
+    FloodSmem<L> &s = *reinterpret_cast<FloodSmem<L> *>(smem_raw);
+    DevExec<RG_PASSC_THREADS> ex; ex.tmap = &tmap;
     if (P.use_tma) ex.mbar_init(&s.mbar);
-    pass_c_list<C>(ex, P, s);
+    pass_c_list<L>(ex, P, s);
 }
 
 template <class C>
@@ -495,7 +499,7 @@ static int set_attrs()
 {
     CK(cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<typename LeanOf<C>::type>)));
     CK(cudaFuncSetAttribute(k_pass_a_full<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem<C>)));
-    CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FloodSmem<C>)));
+    CK(cudaFuncSetAttribute(k_pass_c<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FloodSmem<typename LeanOf<C>::type>)));
     return RG_OK;
 }
 
@@ -579,11 +583,11 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
     if (c->last_is2d) {
         k_flag_tiles<Cfg2D><<<flag_blocks(c->last_ntiles), RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
-        k_pass_c<Cfg2D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg2D>), st>>>(c->last_P, c->last_tmap);
+        k_pass_c<Cfg2D><<<RG_PASSC_CTAS, RG_PASSC_THREADS, sizeof(FloodSmem<LeanOf<Cfg2D>::type>), st>>>(c->last_P, c->last_tmap_fast);
     } else {
         k_flag_tiles<Cfg3D><<<flag_blocks(c->last_ntiles), RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
-        k_pass_c<Cfg3D><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(FloodSmem<Cfg3D>), st>>>(c->last_P, c->last_tmap);
+        k_pass_c<Cfg3D><<<RG_PASSC_CTAS, RG_PASSC_THREADS, sizeof(FloodSmem<LeanOf<Cfg3D>::type>), st>>>(c->last_P, c->last_tmap_fast);
     }
     if (c->profile) cudaEventRecord(c->ev[6], st);
     CK(cudaGetLastError());

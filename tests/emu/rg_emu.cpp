@@ -103,10 +103,11 @@ template <class C> static void emu_label(EmuState &E)
 template <class C> static void emu_finish(EmuState &E)
 {
     HostExec ex; const Params &P = E.P;
-    FloodSmem<C> *s = (FloodSmem<C> *)aligned_alloc(128, (sizeof(FloodSmem<C>) + 127) / 128 * 128);
+    typedef typename LeanOf<C>::type LC;                             /* pass C stages in the lean layout, as the kernel does */
+    FloodSmem<LC> *s = (FloodSmem<LC> *)aligned_alloc(128, (sizeof(FloodSmem<LC>) + 127) / 128 * 128);
     flag_tiles_all<C>(ex, P);
     memset(s, 0x5A, sizeof *s);
-    pass_c_list<C>(ex, P, *s);
+    pass_c_list<LC>(ex, P, *s);
     free(s);
 }
 
