@@ -90,7 +90,8 @@ struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint16_t cnt[6];             /* face-list lengths, order XM XP YM YP ZM ZP */
     uint16_t uniform;            /* 1: all voxels of the tile are one component (pass C needs no image read) */
     uint16_t pad1;
-    uint32_t pad2, pad3;
+    uint32_t plane_slot1;        /* 1 + index of the tile's saved link planes (Params::planes), 0 = none */
+    uint32_t pad3;
 };
 
 struct Params {
@@ -115,6 +116,8 @@ struct Params {
     uint32_t node_cap;
     uint32_t *complex_list;      /* tiles the fast labelling pass handed to the full one */
     uint32_t *flag_list;         /* tiles that hold part of the region (pass C work list) */
+    uint32_t *planes;            /* [plane_cap][3][NW] link planes (ex, ey, ez) the full pass saves for pass C; may be null */
+    uint32_t plane_cap;          /* how many tiles' planes fit */
     int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tiles_all then stores no zeros */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
@@ -152,7 +155,9 @@ struct alignas(128) TileSmem {
         parent_t parent[C::NV];                    /* run union-find (image is dead by then) */
     } u;
     uint64_t mbar;                                 /* TMA completion barrier */
-    uint32_t ex[C::NW], ey[C::NW], ez[C::NW];      /* bit i: voxel i similar to its +x/+y/+z neighbour (in-tile) */
+    alignas(16) uint32_t ex[C::NW];                /* bit i: voxel i similar to its +x/+y/+z neighbour (in-tile); 16-byte */
+    alignas(16) uint32_t ey[C::NW];                /* aligned: they are copied out 16 bytes at a time for pass C */
+    alignas(16) uint32_t ez[C::NW];
     uint32_t fmask[C::FW_TOTAL];                   /* cross-tile edges per face, de-duplicated */
     uint16_t fprefix[C::FW_TOTAL + 2];
     uint16_t ent_root[C::ENT_MAX];
@@ -161,7 +166,7 @@ struct alignas(128) TileSmem {
     uint32_t scal[16];
     uint32_t scan_scratch[40];
 };
-enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8, SC_NSLOW = 9, SC_CNT0 = 16 };
+enum { SC_SEED_LO = 0, SC_SEED_HI = 1, SC_NODE_BASE = 2, SC_NNODES = 3, SC_ETOT = 4, SC_OVERFLOW = 5, SC_ANY = 6, SC_COMPLEX = 7, SC_UNIFORM = 8, SC_NSLOW = 9, SC_PLANE1 = 10, SC_CNT0 = 16 };
 
 /* ---------------------------------------------------------------- small helpers */
 RG_FN uint32_t valid_bits(int64_t n) { return n >= 32 ? 0xFFFFFFFFu : n <= 0 ? 0u : ((1u << n) - 1u); }
@@ -553,14 +558,14 @@ RG_FN void emit_nodes(Exec &ex, const Params &P, uint32_t tile, S &s)
         TileRec rc;
         rc.node_base = base; rc.nnodes = ok ? k : 0u;
         for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]) : (uint16_t)0;
-        rc.uniform = (uint16_t)(ok ? s.scal[SC_UNIFORM] : 0u); rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
+        rc.uniform = (uint16_t)(ok ? s.scal[SC_UNIFORM] : 0u); rc.pad1 = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
         P.rec[tile] = rc;
     }
 }
 
 /* ================================================================ pass A */
 template <class C, class Exec>
-RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
+RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s, uint32_t plane_slot = 0xFFFFFFFFu)
 {
     int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
@@ -577,6 +582,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
         int a = lo; hi = P.nseeds;
         while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
         s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0; s.scal[SC_UNIFORM] = 0;
+        s.scal[SC_PLANE1] = (P.planes && plane_slot < P.plane_cap) ? plane_slot + 1u : 0u;
     }
     if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
     ex.tile_wait(&s.mbar);
@@ -585,6 +591,16 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
     build_edges<C, true>(ex, P, s.u.i.img, s.ex, s.ey, s.ez, s.fmask, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 11) return;
+    if (P.planes && plane_slot < P.plane_cap) {
+        /* pass C needs exactly these three planes if the tile turns out to hold region voxels: 12 KB kept in place of
+           a second 49 KB stage + the byte-SIMD comparison of every voxel pair */
+        uint32_t *dst = P.planes + (size_t)plane_slot * 3 * C::NW;
+        ex.pfor(3 * C::NW / 4, [&](int i) {
+            const int pl = i / (C::NW / 4), k = i % (C::NW / 4);
+            const uint32_t *src = pl == 0 ? s.ex : pl == 1 ? s.ey : s.ez;
+            st128(dst + (size_t)pl * C::NW + 4 * k, ld128(src + 4 * k));
+        });
+    }
     label_runs<C>(ex, s);
     if (P.debug_stop == 12) return;
 
@@ -728,8 +744,15 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     const TileRec rc = P.rec[tile];
 
     if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
-    const bool tma = ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0);
-    if (!tma) load_tile<C>(ex, P, s.u.img, x0, y0, z0, false);
+    const bool saved = P.planes && rc.plane_slot1;                  /* the full pass kept this tile's link planes */
+    if (saved) {
+        const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;
+        ex.pfor(3 * C::NW / 4, [&](int i) {
+            const int pl = i / (C::NW / 4), k = i % (C::NW / 4);
+            uint32_t *dst = pl == 0 ? s.ex : pl == 1 ? s.ey : s.ez;
+            st128(dst + 4 * k, ld128(src + (size_t)pl * C::NW + 4 * k));
+        });
+    } else if (!ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.img, x0, y0, z0, false);
     ex.pfor(C::NW / 4, [&](int i) { st128(&s.M[4 * i], u32x4{0, 0, 0, 0}); });
     if (ex.tid() == 0) s.scal[SC_ANY] = 0;
     ex.sync();
@@ -745,8 +768,10 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     ex.sync();
     if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
     if (P.debug_stop == 20) return;
-    build_edges<C, false>(ex, P, s.u.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
-    ex.sync();
+    if (!saved) {
+        build_edges<C, false>(ex, P, s.u.img, s.ex, s.ey, s.ez, (uint32_t *)0, x0, y0, z0);
+        ex.sync();
+    }
     if (P.debug_stop == 21) return;
     /* A region advances a whole run per sweep in x but one row / plane per sweep in y and z, so a tile that is still
        changing after a few sweeps (a solid: up to TY + TZ of them) gets stride planes and continues 1, 2, 4, ...

@@ -347,6 +347,7 @@ struct rg_ctx {
     uint32_t *last_counters;                   /* device counters of the last call */
     cudaStream_t last_stream;
     bool attr_set;
+    bool may_grow;                             /* the context owns its scratch and may enlarge it (not the noalloc view) */
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
     ResolveArgs *d_rargs;                      /* device copy of the exchange bookkeeping (optimistic exchange) */
@@ -391,6 +392,7 @@ static bool make_tmap(CUtensorMap *tm, const uint8_t *base, int64_t nx, int64_t 
 
 struct Layout {
     size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, off_rargs, total;
+    size_t off_planes, total_with_planes; uint32_t plane_cap;      /* optional tail: link planes the full pass keeps for pass C */
     uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
 };
 
@@ -433,6 +435,11 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
     L.off_flist = o; o = align_up(o + (size_t)ntiles * 4, 256);
     L.off_rargs = o; o = align_up(o + sizeof(ResolveArgs), 256);
     L.total = o;
+    /* optional: 12 KB of link planes for each of the first plane_cap tiles of the full pass's list (all of them up to
+       64 Ki tiles).  A context takes it if the allocation succeeds; rg_workspace_bytes does not count it. */
+    L.plane_cap = (uint32_t)(ntiles < 65536 ? ntiles : 65536);
+    L.off_planes = o; o = align_up(o + (size_t)L.plane_cap * 3 * C::NW * sizeof(uint32_t), 256);
+    L.total_with_planes = o;
     return RG_OK;
 }
 
@@ -459,6 +466,7 @@ extern "C" int rg_ctx_create(int device, rg_ctx **out)
     rg_ctx *c = (rg_ctx *)calloc(1, sizeof(rg_ctx));
     if (!c) return fail(RG_ERR_NOMEM, "calloc");
     c->device = device;
+    c->may_grow = true;
     e = cudaHostAlloc((void **)&c->h_status, CTR_WORDS * sizeof(uint32_t), cudaHostAllocDefault);
     if (e != cudaSuccess) { free(c); return fail(RG_ERR_CUDA, "cudaHostAlloc", e); }
     *out = c;
@@ -491,6 +499,8 @@ extern "C" int rg_ctx_reserve(rg_ctx *c, int64_t nx, int64_t ny, int64_t nz, int
     if (!c || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0) return fail(RG_ERR_ARG, "bad argument");
     Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
     if (rc) return rc;
+    if (ensure_ws(c, L.total_with_planes) == RG_OK) return RG_OK;      /* with the optional link-plane tail if it fits */
+    g_err[0] = 0; cudaGetLastError();
     return ensure_ws(c, L.total);
 }
 
@@ -537,6 +547,8 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
     P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
     P.complex_list = (uint32_t *)(ws + L.off_clist); P.flag_list = (uint32_t *)(ws + L.off_flist);
+    const bool have_planes = c->ws_bytes >= L.total_with_planes && !getenv("RG_NO_PLANES");
+    P.planes = have_planes ? (uint32_t *)(ws + L.off_planes) : nullptr; P.plane_cap = have_planes ? L.plane_cap : 0u;
     uint64_t *keys = (uint64_t *)(ws + L.off_keys), *keys2 = (uint64_t *)(ws + L.off_keys2);
     P.seed_keys = keys;
 
@@ -608,6 +620,8 @@ static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int6
     }
     Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
     if (rc) return rc;
+    /* with the optional tail if the memory is there (a context that was given its scratch, the noalloc view, keeps what it has) */
+    if (c->ws_bytes < L.total_with_planes && c->may_grow) { if (ensure_ws(c, L.total_with_planes) != RG_OK) { g_err[0] = 0; cudaGetLastError(); } }
     rc = ensure_ws(c, L.total); if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     return nz == 1 ? launch_label<Cfg2D>(c, L, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, st)

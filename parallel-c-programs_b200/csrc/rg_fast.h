@@ -343,7 +343,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         TileRec rc;
         rc.node_base = base; rc.nnodes = nnodes;
         for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)s.scal[SC_CNT0 + f];
-        rc.uniform = uniform ? 1 : 0; rc.pad1 = 0; rc.pad2 = rc.pad3 = 0;
+        rc.uniform = uniform ? 1 : 0; rc.pad1 = 0; rc.plane_slot1 = 0; rc.pad3 = 0;
         P.rec[tile] = rc;
     }
 }
@@ -354,7 +354,7 @@ RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
 {
     const uint32_t n = P.counters[CTR_NCOMPLEX];
     for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
-        tile_pass_a<C>(ex, P, P.complex_list[i], s);
+        tile_pass_a<C>(ex, P, P.complex_list[i], s, i);             /* list position = slot of the saved link planes */
         ex.sync();
     }
 }

@@ -22,6 +22,8 @@
 #define RG_HDFN static inline
 #define RG_DEVICE_BUILD 0
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
 #endif
 
 namespace rg {
@@ -105,8 +107,10 @@ RG_FN uint16_t ldv16(const uint16_t *p) { return *p; }
 RG_FN uint32_t ldv32(const uint32_t *p) { return *p; }
 RG_FN void stv16(uint16_t *p, uint16_t v) { *p = v; }
 RG_FN void stv32(uint32_t *p, uint32_t v) { *p = v; }
-RG_FN u32x4 ld128(const void *p) { u32x4 v; memcpy(&v, p, 16); return v; }
-RG_FN void st128(void *p, u32x4 v) { memcpy(p, &v, 16); }
+/* the device versions are single 16-byte accesses and fault on a misaligned address: the CPU walk checks the same */
+RG_FN void check16(const void *p) { if ((uintptr_t)p & 15u) { fprintf(stderr, "rg emulator: misaligned 16-byte access at %p\n", p); abort(); } }
+RG_FN u32x4 ld128(const void *p) { check16(p); u32x4 v; memcpy(&v, p, 16); return v; }
+RG_FN void st128(void *p, u32x4 v) { check16(p); memcpy(p, &v, 16); }
 RG_FN u32x4 ld128_stream(const void *p) { return ld128(p); }
 RG_FN void st128_stream(void *p, u32x4 v) { st128(p, v); }
 #endif

@@ -52,12 +52,14 @@ struct HostExec {
     }
 };
 
-static int g_force_full = 0;      /* 1: label every tile with the full pass (fast pass off) */
+static int g_force_full = 0;
+static int g_no_planes = 0;      /* 1: label every tile with the full pass (fast pass off) */
 extern "C" void emu_force_full(int v) { g_force_full = v; }
+extern "C" void emu_no_planes(int v) { g_no_planes = v; }
 
 struct EmuState {
     std::vector<TileRec> rec; std::vector<uint16_t> ent; std::vector<uint32_t> npar; std::vector<uint16_t> nrep;
-    std::vector<uint64_t> keys; std::vector<uint32_t> clist, flist; uint32_t counters[CTR_WORDS];
+    std::vector<uint64_t> keys; std::vector<uint32_t> clist, flist, planes; uint32_t counters[CTR_WORDS];
     Params P;
 };
 
@@ -78,6 +80,10 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     E.keys.assign((size_t)std::max(nseeds, 1), ~0ull);
     E.clist.assign(ntiles, 0); E.flist.assign(ntiles, 0);
     P.complex_list = E.clist.data(); P.flag_list = E.flist.data();
+    /* link planes kept by the full pass for pass C: room for every second tile, so that both branches of pass C run */
+    P.plane_cap = g_no_planes ? 0u : (uint32_t)((ntiles + 1) / 2);
+    E.planes.assign((size_t)P.plane_cap * 3 * C::NW + 4, 0xDEADBEEFu);
+    P.planes = P.plane_cap ? E.planes.data() : nullptr;
     P.rec = E.rec.data(); P.ent = E.ent.data(); P.nparent = E.npar.data(); P.nrep = E.nrep.data();
     P.counters = E.counters; P.node_cap = (uint32_t)cap; P.nseeds = nseeds; P.seed_keys = E.keys.data();
     HostExec ex;

@@ -179,6 +179,22 @@ def test_emu_fast_and_full_paths_mix(emu, oracle):
     assert int(st2[0]) == int(st[0])                      # same number of coarse nodes whichever path labelled the tiles
 
 
+def test_emu_saved_link_planes_do_not_change_the_result(emu, oracle):
+    """the full pass keeps the link planes of the tiles it labels and pass C floods from them instead of staging the
+    tile again; the emulator keeps room for every second such tile, so both branches run -- and with no room at all
+    the result is the same"""
+    img, seeds, T = oracle.synth("c3", 40)
+    want = oracle.grow(img, seeds, T)
+    got, st = run_emu(emu, 1, img, seeds, T)
+    assert (got == want).all() and int(st[2]) > 2                   # several tiles went through the full pass
+    emu.emu_no_planes(1)
+    try:
+        got2, _ = run_emu(emu, 1, img, seeds, T)
+    finally:
+        emu.emu_no_planes(0)
+    assert (got2 == want).all()
+
+
 @pytest.mark.parametrize("levels", [2, 4, 12, 40])
 def test_emu_walk_limit_boundary(emu, oracle, levels):
     """component sizes around WALK_MAX: some walks overflow, some do not"""
