@@ -39,31 +39,36 @@ template <class C>
 struct alignas(128) FastSmem {
     uint8_t img[C::IMG_BYTES];
     uint64_t mbar;
-    /* the cross-tile edge words and their prefix sums are dead once the edge list exists; the list of the longer
-       walks, written after that, takes their place */
+    /* Storage shared over time.  The cross-tile edge words and their prefix sums are dead once the edge list exists and the
+       list of the longer walks takes their place; that list and the x = TX halo column (lean layout: one byte per (y, z),
+       used by the face masks only) are dead once the walks are done, and the dense node ids of the slots go there. */
     union {
-        struct { uint32_t fmask[C::FW_TOTAL]; uint16_t fprefix[C::FW_TOTAL + 2]; } f;
-        uint16_t slow[FAST_ENT_MAX];              /* edges whose start voxel has a similar neighbour inside the tile */
-    } u;
+        struct {
+            union {
+                struct { uint32_t fmask[C::FW_TOTAL]; uint16_t fprefix[C::FW_TOTAL + 2]; } f;
+                uint16_t slow[FAST_ENT_MAX];      /* edges whose start voxel has a similar neighbour inside the tile */
+            } u;
+            uint8_t xr[C::XR ? 16 : C::TY * C::TZ];
+        } e;
+        uint16_t slotid[HASH_N];                  /* dense node id of each occupied slot (scan after the walks) */
+    } v;
     uint16_t ent_root[FAST_ENT_MAX];              /* per edge: start voxel, later the hash slot of its component */
-    alignas(16) uint16_t tab[HASH_N];             /* open addressing: representative + 1 (<= 32768), 0 = empty */
-    uint16_t slotid[HASH_N];                      /* dense node id of each occupied slot (scan after the walks) */
+    alignas(16) uint32_t tab[HASH_N];             /* open addressing: representative + 1, 0 = empty (32-bit: shared-memory CAS is native) */
     alignas(16) uint32_t seedtab[HASH_N / 32];    /* bit per slot: the component holds a seed */
-    uint8_t xr[C::XR ? 16 : C::TY * C::TZ];       /* lean layout: the x = TX halo column, one byte per (y, z) */
     uint32_t scal[24];                            /* SC_* and, from SC_CNT0 on, the six face-list lengths */
     uint32_t scan_scratch[40];
-    static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit; hash keys are 16 bits");
+    static_assert(C::NV <= 32768, "walk queue entries are 15-bit voxel indices + a valid bit");
 };
 
 /* find or insert representative `root`; returns its slot.  Dense node ids are handed out afterwards by one
    scan over the slots (a shared counter bumped by every inserting thread serialises the whole phase). */
-RG_FN uint32_t hash_slot(uint16_t *tab, uint32_t *scal, uint32_t root)
+RG_FN uint32_t hash_slot(uint32_t *tab, uint32_t *scal, uint32_t root)
 {
     const uint32_t key = root + 1u;
     uint32_t slot = (root * 2654435761u) >> (32 - HASH_BITS);
     for (int probe = 0; probe < HASH_N; probe++) {
-        uint32_t cur = ldv16(&tab[slot]);
-        if (cur == 0u) cur = cas16(&tab[slot], (uint16_t)0, (uint16_t)key);
+        uint32_t cur = ldv32(&tab[slot]);
+        if (cur == 0u) cur = cas32(&tab[slot], 0u, key);
         if (cur == 0u || cur == key) return slot;
         slot = (slot + 1u) & (HASH_N - 1);
     }
@@ -231,15 +236,15 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
 
     if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
     if (P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);          /* fire-and-forget stores: they fill the load's latency */
-    ex.pfor(C::FW_TOTAL, [&](int i) { s.u.f.fmask[i] = 0; });
-    ex.pfor(HASH_N / 8, [&](int i) { st128(&s.tab[8 * i], u32x4{0, 0, 0, 0}); });
+    ex.pfor(C::FW_TOTAL, [&](int i) { s.v.e.u.f.fmask[i] = 0; });
+    ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
     if (!C::XR) {
         /* lean layout: the x = TX column is not in the staged box; one byte per (y, z) straight from the image (the
            neighbouring tile's CTA reads the same lines, so these come from L2) */
         const bool has_col = x0 + C::TX < P.nx;
         ex.pfor(C::TY * C::TZ, [&](int q) {
             const int y = q % C::TY, z = q / C::TY;
-            s.xr[q] = (has_col && y < vy && z < vz) ? P.image[((z0 + z) * P.ny + (y0 + y)) * P.nx + x0 + C::TX] : (uint8_t)0;
+            s.v.e.xr[q] = (has_col && y < vy && z < vz) ? P.image[((z0 + z) * P.ny + (y0 + y)) * P.nx + x0 + C::TX] : (uint8_t)0;
         });
     }
     ex.pfor(HASH_N / 32, [&](int i) { s.seedtab[i] = 0; });
@@ -267,13 +272,13 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             uniform = !ex.sync_or(differs);
         }
     }
-    build_face_masks<C>(ex, P, s.img, s.xr, s.u.f.fmask, x0, y0, z0);
+    build_face_masks<C>(ex, P, s.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 3) return;
-    const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.u.f.fmask[i]); }, s.u.f.fprefix, s.scan_scratch);
+    const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.v.e.u.f.fmask[i]); }, s.v.e.u.f.fprefix, s.scan_scratch);
     if (ex.tid() == 0) {
-        s.u.f.fprefix[C::FW_TOTAL] = (uint16_t)etot;
-        for (int f = 0; f < 6; f++) s.scal[SC_CNT0 + f] = (uint32_t)(s.u.f.fprefix[C::fw_off(f + 1)] - s.u.f.fprefix[C::fw_off(f)]);   /* the prefix sums do not live to the end */
+        s.v.e.u.f.fprefix[C::FW_TOTAL] = (uint16_t)etot;
+        for (int f = 0; f < 6; f++) s.scal[SC_CNT0 + f] = (uint32_t)(s.v.e.u.f.fprefix[C::fw_off(f + 1)] - s.v.e.u.f.fprefix[C::fw_off(f)]);   /* the prefix sums do not live to the end */
     }
     const bool seeded = s.scal[SC_SEED_HI] > s.scal[SC_SEED_LO];
     const uint32_t base = fast_node_base(tile);
@@ -287,11 +292,11 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         if (etot > (uint32_t)FAST_ENT_MAX) { fast_give_up<C>(ex, P, tile); return; }     /* same total in every thread */
         /* start voxel of every cross-tile edge, in list order ... */
         ex.pfor(C::FW_TOTAL, [&](int fw) {
-            uint32_t m = s.u.f.fmask[fw];
+            uint32_t m = s.v.e.u.f.fmask[fw];
             if (!m) return;
             int f = 0; while (fw >= C::fw_off(f + 1)) f++;
             const int idx = fw - C::fw_off(f);
-            uint32_t slot = s.u.f.fprefix[fw];
+            uint32_t slot = s.v.e.u.f.fprefix[fw];
             while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vy, vz); }
         });
         ex.sync();
@@ -299,7 +304,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
            own component; the others go to a compact list so that the longer walks fill whole warps. */
         ex.pfor((int)etot, [&](int e) {
             const uint32_t v = s.ent_root[e];
-            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
+            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.v.e.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
             else s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, v);
         });
         {
@@ -315,7 +320,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         ex.sync();
         if (P.debug_stop == 6) return;
         ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
-            const int e = s.u.slow[i];
+            const int e = s.v.e.u.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
             const uint32_t nb0 = neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v);
@@ -328,13 +333,13 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         if (P.debug_stop == 7 || P.debug_stop == 61 || P.debug_stop == 62) return;
         if (s.scal[SC_COMPLEX]) { fast_give_up<C>(ex, P, tile); return; }
         /* dense ids in slot order, then face lists and nodes go out in one sweep */
-        nnodes = ex.scan16(HASH_N, [&](int i) { return s.tab[i] ? 1u : 0u; }, s.slotid, s.scan_scratch);
+        nnodes = ex.scan16(HASH_N, [&](int i) { return s.tab[i] ? 1u : 0u; }, s.v.slotid, s.scan_scratch);
         if (nnodes > (uint32_t)HASH_MAX_KEYS) { fast_give_up<C>(ex, P, tile); return; }
-        ex.pfor((int)etot, [&](int e) { ent[e] = s.slotid[s.ent_root[e]]; });
+        ex.pfor((int)etot, [&](int e) { ent[e] = s.v.slotid[s.ent_root[e]]; });
         ex.pfor(HASH_N, [&](int slot) {
             const uint32_t cur = s.tab[slot];
             if (!cur) return;
-            const uint32_t g = base + s.slotid[slot];
+            const uint32_t g = base + s.v.slotid[slot];
             P.nparent[g] = ((s.seedtab[slot >> 5] >> (slot & 31)) & 1u) ? 0u : g;      /* seeded components start hooked to node 0 */
             P.nrep[g] = (uint16_t)(cur - 1u);
         });
