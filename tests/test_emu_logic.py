@@ -226,3 +226,28 @@ def test_emu_uniform_tiles(emu, oracle, cfg):
     # threshold 0: no edges at all, the shortcut must not fire
     got3, _ = run_emu(emu, cfg, img, seeds, 0)
     assert got3.sum() == 3
+
+
+def test_emu_random_stress(emu, oracle):
+    """many small random cases in one go: shapes around the tile sizes of the three emulator configurations (ragged in
+    every axis), 2 to 40 grey levels, thresholds 0 to 300, seeds inside, outside and duplicated, single- and multi-slab"""
+    rng = np.random.default_rng(20240607)
+    for case in range(120):
+        cfg = int(rng.integers(1, 3))
+        if rng.random() < 0.3:
+            shape = (int(rng.integers(1, 40)), int(rng.integers(1, 140)))
+        else:
+            shape = (int(rng.integers(1, 14)), int(rng.integers(1, 22)), int(rng.integers(1, 140)))
+        levels = int(rng.choice([2, 3, 5, 12, 40]))
+        T = int(rng.choice([0, 1, 1, 2, 3, 17, 255, 256, 300]))
+        img, seeds = rand_case(rng, shape, levels, int(rng.integers(0, 7)))
+        if len(seeds) > 1 and rng.random() < 0.3:
+            seeds[-1] = seeds[0]
+        want = oracle.grow(img, seeds, T)
+        got, _ = run_emu(emu, cfg, img, seeds, T)
+        assert (got == want).all(), (case, cfg, shape, levels, T)
+        axis_len = shape[0]
+        G = int(rng.integers(2, 5))
+        if axis_len >= 2 * G:                                       # every logical rank needs two planes / rows
+            got, _ = run_emu(emu, cfg, img, seeds, T, slabs=G)
+            assert (got == want).all(), ("slabs", case, cfg, shape, levels, T, G)
