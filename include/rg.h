@@ -107,9 +107,16 @@ int rg_grow_device(rg_ctx *ctx, const uint8_t *d_image, int64_t nx, int64_t ny, 
 int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_t ny, int64_t nz,
                            const int32_t *d_seeds_xyz, int nseeds, int threshold, uint8_t *d_mask, void *stream);
 int64_t rg_noalloc_scratch_bytes(void);
+/* No counterpart in the reference.  The engine's self-check for the last rg_grow_device_noalloc on the current device:
+ * waits for `stream` (pass the one the grow ran on), then returns RG_OK or RG_ERR_INTERNAL like rg_ctx_status and
+ * fills stats (may be NULL) the same way.  Allocates nothing.  The scratch of that entry point is always sized for the
+ * worst case (it ignores RG_NODE_BUDGET), so "out of node ids" cannot happen there; what this reports is the
+ * face-list cross-check of the labelling passes. */
+int rg_noalloc_status(uint32_t stats[4], void *stream);
 
 /* Synchronises the stream last used and returns RG_OK or RG_ERR_INTERNAL / RG_ERR_CUDA;
- * stats (may be NULL) receives {coarse nodes, status bits, tiles labelled by the full pass, tiles holding region voxels}. */
+ * stats (may be NULL) receives {coarse nodes, status bits, tiles the bounded walkers did not get through (labelled by the
+ * dense path or the full pass), tiles holding region voxels}. */
 int rg_ctx_status(rg_ctx *ctx, uint32_t stats[4]);
 
 /* Optional per-kernel timing with CUDA events on the launching stream (used by bench.py for the

@@ -31,7 +31,9 @@
 namespace rg {
 
 enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
-enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_WORDS = 8 };
+enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_NPLANES = 5, CTR_NDENSE = 6, CTR_WORDS = 8 };
+/* CTR_NCOMPLEX: tiles listed for the full labelling pass; CTR_NDENSE: tiles the in-CTA dense path labelled (rg_dense.h);
+   CTR_NPLANES: link-plane slots handed out (both of those passes keep a tile's planes for pass C) */
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
 /* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
@@ -119,6 +121,7 @@ struct Params {
     uint32_t *planes;            /* [plane_cap][3][NW] link planes (ex, ey, ez) the full pass saves for pass C; may be null */
     uint32_t plane_cap;          /* how many tiles' planes fit */
     int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tiles_all then stores no zeros */
+    int32_t force_dense;         /* testing aid (env RG_FORCE_DENSE): the fast labelling pass sends every non-uniform tile down its dense path */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
@@ -188,11 +191,12 @@ RG_FN uint32_t edge_word(const uint32_t a[8], const uint32_t b[8], int tmode, ui
 {
     if (tmode == 0) return 0u;
     if (tmode == 2) return 0xFFFFFFFFu;
+    const ByteCmp k = byte_cmp_for(t4 & 0xFFu);                /* depends on the launch only: hoisted out of every loop */
     uint32_t w = 0;
 #if RG_DEVICE_BUILD
 #pragma unroll
 #endif
-    for (int j = 0; j < 8; j++) w |= edge4(a[j], b[j], t4) << (4 * j);
+    for (int j = 7; j >= 0; j--) w = funnel_l(lt4_top_nibble(a[j], b[j], k), w, 4);   /* (w << 4) | nibble, one SHF each */
     return w;
 }
 RG_FN bool similar1(uint32_t a, uint32_t b, int tmode, uint32_t t4)
@@ -273,6 +277,17 @@ RG_FN void tile_origin(const Params &P, uint32_t tile, int &tx, int &ty, int &tz
 
 /* staged position of tile-local voxel (x,y,z), -1 <= x <= TX, -1 <= y <= TY, -HZ <= z <= TZ-1+HZ */
 template <class C> RG_FN int img_off(int x, int y, int z) { return ((z + C::HZ) * C::PY + (y + 1)) * C::RS + C::XO + x; }
+
+/* voxel (tile-local linear index) on this side of cross-tile edge `b` of face word (f, idx) */
+template <class C>
+RG_FN uint32_t face_voxel(int f, int idx, int b, int vy, int vz)
+{
+    int x, y, z;
+    if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
+    else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? vy - 1 : 0; }
+    else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
+    return (uint32_t)((z * C::TY + y) * C::TX + x);
+}
 
 /* ---------------------------------------------------------------- stage a tile in shared memory */
 template <class C, class Exec>
@@ -565,7 +580,7 @@ RG_FN void emit_nodes(Exec &ex, const Params &P, uint32_t tile, S &s)
 
 /* ================================================================ pass A */
 template <class C, class Exec>
-RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s, uint32_t plane_slot = 0xFFFFFFFFu)
+RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
 {
     int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
     const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
@@ -582,7 +597,9 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s,
         int a = lo; hi = P.nseeds;
         while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
         s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0; s.scal[SC_UNIFORM] = 0;
-        s.scal[SC_PLANE1] = (P.planes && plane_slot < P.plane_cap) ? plane_slot + 1u : 0u;
+        uint32_t p1 = 0;                                        /* a slot for this tile's link planes (shared with the dense path) */
+        if (P.planes) { const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u); if (slot < P.plane_cap) p1 = slot + 1u; }
+        s.scal[SC_PLANE1] = p1;
     }
     if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
     ex.tile_wait(&s.mbar);
@@ -591,10 +608,10 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s,
     build_edges<C, true>(ex, P, s.u.i.img, s.ex, s.ey, s.ez, s.fmask, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 11) return;
-    if (P.planes && plane_slot < P.plane_cap) {
+    if (s.scal[SC_PLANE1]) {
         /* pass C needs exactly these three planes if the tile turns out to hold region voxels: 12 KB kept in place of
            a second 49 KB stage + the byte-SIMD comparison of every voxel pair */
-        uint32_t *dst = P.planes + (size_t)plane_slot * 3 * C::NW;
+        uint32_t *dst = P.planes + (size_t)(s.scal[SC_PLANE1] - 1u) * 3 * C::NW;
         ex.pfor(3 * C::NW / 4, [&](int i) {
             const int pl = i / (C::NW / 4), k = i % (C::NW / 4);
             const uint32_t *src = pl == 0 ? s.ex : pl == 1 ? s.ey : s.ez;

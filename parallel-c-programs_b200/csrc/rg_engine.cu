@@ -74,10 +74,18 @@ struct DevExec {
             tma_pending = false;
         }
     }
+    static constexpr int NTHREADS = NT;
     __device__ __forceinline__ int tid() const { return (int)threadIdx.x; }
     template <class F> __device__ __forceinline__ void pfor(int n, F f)
     {
         for (int i = (int)threadIdx.x; i < n; i += NT) f(i);
+    }
+    /* the same split, f(i, k) with k = 0, 1, ... counting this thread's items: two pfor_k over the same n hand a
+       thread the same items, so per-thread arrays indexed by k carry values across a barrier in registers */
+    template <class F> __device__ __forceinline__ void pfor_k(int n, F f)
+    {
+#pragma unroll
+        for (int k = 0; k < (n + NT - 1) / NT; k++) { const int i = (int)threadIdx.x + k * NT; if (i < n) f(i, k); }
     }
     /* one warp per item: pred(item, lane) is OR-ed over the warp and handed to body(item, lane, any) */
     template <class Pr, class Bo> __device__ __forceinline__ void wfor(uint32_t n, Pr pred, Bo body)
@@ -348,6 +356,8 @@ struct rg_ctx {
     cudaStream_t last_stream;
     bool attr_set;
     bool may_grow;                             /* the context owns its scratch and may enlarge it (not the noalloc view) */
+    bool worst_case_layout;                    /* size the node space for the worst case whatever RG_NODE_BUDGET says (the noalloc view) */
+    size_t tail_refused;                       /* smallest size for which the optional link-plane tail did not fit (0 = never failed) */
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
     ResolveArgs *d_rargs;                      /* device copy of the exchange bookkeeping (optimistic exchange) */
@@ -355,23 +365,24 @@ struct rg_ctx {
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     CUtensorMap last_tmap_fast;                /* the same image with the lean box of the fast labelling pass */
     bool profile; cudaEvent_t ev[7]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
+    uint32_t last_full_tiles;                      /* tiles of the last call that overflowed the dense path (set by rg_ctx_status) */
 };
 
 /* cuTensorMapEncodeTiled through the runtime, so the library does not link against libcuda */
 typedef CUresult (*tmap_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn lookup_tmap_encoder()
+{
+    void *p = nullptr; cudaDriverEntryPointQueryResult q;
+    if (getenv("RG_NO_TMA")) return nullptr;                /* debugging aid: force the cp.async staging path */
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+        return (tmap_encode_fn)p;
+    return nullptr;
+}
 static tmap_encode_fn get_tmap_encoder()
 {
-    static tmap_encode_fn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void *p = nullptr; cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
-            fn = (tmap_encode_fn)p;
-        if (getenv("RG_NO_TMA")) fn = nullptr;              /* debugging aid: force the cp.async staging path */
-    }
+    static const tmap_encode_fn fn = lookup_tmap_encoder(); /* function-local static: initialised once, also with several host threads */
     return fn;
 }
 
@@ -399,7 +410,7 @@ struct Layout {
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 template <class C>
-static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L)
+static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L, bool honour_env = true)
 {
     int64_t ntx = (nx + C::TX - 1) / C::TX, nty = (ny + C::TY - 1) / C::TY, ntz = (nz + C::TZ - 1) / C::TZ;
     int64_t ntiles = ntx * nty * ntz;
@@ -408,7 +419,7 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
        is full; beyond that -- or when RG_NODE_BUDGET says so -- the full pass gets an average of RG_NODE_BUDGET (2048)
        nodes per tile.  Running out is detected on the device (status bit 1, rg_ctx_status fails), never silent. */
     int64_t budget = (int64_t)C::ENT_MAX;
-    { const char *e = getenv("RG_NODE_BUDGET"); if (e && atoll(e) > 0 && atoll(e) < budget) budget = atoll(e); }
+    if (honour_env) { const char *e = getenv("RG_NODE_BUDGET"); if (e && atoll(e) > 0 && atoll(e) < budget) budget = atoll(e); }
     int64_t node_cap = 1 + ntiles * (budget + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
     if (node_cap >= (1ll << 32)) node_cap = 1 + ntiles * ((budget < 2048 ? budget : 2048) + (int64_t)FAST_NODE_SLOTS) + (int64_t)nseeds;
     if (ntiles >= (1ll << 31) || node_cap >= (1ll << 32)) return fail(RG_ERR_TOO_LARGE, "volume too large for 32-bit node ids");
@@ -443,9 +454,9 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
     return RG_OK;
 }
 
-static int layout_for(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L)
+static int layout_for(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L, bool honour_env = true)
 {
-    return nz == 1 ? make_layout<Cfg2D>(nx, ny, nz, nseeds, L) : make_layout<Cfg3D>(nx, ny, nz, nseeds, L);
+    return nz == 1 ? make_layout<Cfg2D>(nx, ny, nz, nseeds, L, honour_env) : make_layout<Cfg3D>(nx, ny, nz, nseeds, L, honour_env);
 }
 
 extern "C" int64_t rg_workspace_bytes(int64_t nx, int64_t ny, int64_t nz, int nseeds)
@@ -483,14 +494,30 @@ extern "C" void rg_ctx_destroy(rg_ctx *c)
     free(c);
 }
 
-static int ensure_ws(rg_ctx *c, size_t bytes)
+/* Grow the context's scratch to `bytes`.  The larger block is allocated FIRST and the old one freed only when that
+   worked, so a failed attempt leaves the context as it was (nothing to synchronise, nothing lost).  `required` = false
+   is the optional link-plane tail: its failure is remembered per size and not retried on every call. */
+static int ensure_ws(rg_ctx *c, size_t bytes, bool required = true)
 {
     if (bytes <= c->ws_bytes) return RG_OK;
+    if (!c->may_grow) return fail(RG_ERR_NOMEM, "the scratch of this context is fixed and too small");
+    if (!required && c->tail_refused && bytes >= c->tail_refused) return RG_ERR_NOMEM;
     ON_DEVICE(c->device);
-    if (c->ws) { CK(cudaDeviceSynchronize()); cudaFree(c->ws); c->ws = nullptr; c->ws_bytes = 0; }
-    cudaError_t e = cudaMalloc(&c->ws, bytes);
-    if (e != cudaSuccess) return fail(RG_ERR_NOMEM, "cudaMalloc(workspace)", e);
-    c->ws_bytes = bytes;
+    void *bigger = nullptr;
+    cudaError_t e = cudaMalloc(&bigger, bytes);
+    if (e != cudaSuccess && c->ws && required) {
+        /* not enough room for both: give the old block back and try once more */
+        cudaGetLastError();
+        CK(cudaDeviceSynchronize()); cudaFree(c->ws); c->ws = nullptr; c->ws_bytes = 0;
+        e = cudaMalloc(&bigger, bytes);
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        if (!required) { c->tail_refused = bytes; return RG_ERR_NOMEM; }
+        return fail(RG_ERR_NOMEM, "cudaMalloc(workspace)", e);
+    }
+    if (c->ws) { CK(cudaDeviceSynchronize()); cudaFree(c->ws); }   /* kernels of an earlier call may still use the old block */
+    c->ws = bigger; c->ws_bytes = bytes;
     return RG_OK;
 }
 
@@ -499,8 +526,7 @@ extern "C" int rg_ctx_reserve(rg_ctx *c, int64_t nx, int64_t ny, int64_t nz, int
     if (!c || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0) return fail(RG_ERR_ARG, "bad argument");
     Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
     if (rc) return rc;
-    if (ensure_ws(c, L.total_with_planes) == RG_OK) return RG_OK;      /* with the optional link-plane tail if it fits */
-    g_err[0] = 0; cudaGetLastError();
+    if (ensure_ws(c, L.total_with_planes, false) == RG_OK) return RG_OK;      /* with the optional link-plane tail if it fits */
     return ensure_ws(c, L.total);
 }
 
@@ -537,6 +563,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
     P.nseeds = nseeds;
     { static int dbg = -1; if (dbg < 0) { const char *e = getenv("RG_DEBUG_STOP"); dbg = e ? atoi(e) : 0; } P.debug_stop = dbg; }
+    { static int fd = -1; if (fd < 0) { const char *e = getenv("RG_FORCE_DENSE"); fd = e ? atoi(e) : 0; } P.force_dense = fd; }   /* testing: every non-uniform tile takes the dense path */
     memset(&c->last_tmap, 0, sizeof c->last_tmap);
     /* the tensor map covers the neighbours' halo planes (volumes) or halo rows (images) as well */
     const int64_t ey = ext_ylo<C>(P) + ext_yhi<C>(P), ez = ext_zlo<C>(P) + ext_zhi<C>(P);
@@ -618,11 +645,14 @@ static int label_device_impl(rg_ctx *c, const uint8_t *d_image, int64_t nx, int6
         rc = set_attrs<Cfg2D>(); if (rc) return rc;
         c->attr_set = true;
     }
-    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L, !c->worst_case_layout);
     if (rc) return rc;
-    /* with the optional tail if the memory is there (a context that was given its scratch, the noalloc view, keeps what it has) */
-    if (c->ws_bytes < L.total_with_planes && c->may_grow) { if (ensure_ws(c, L.total_with_planes) != RG_OK) { g_err[0] = 0; cudaGetLastError(); } }
-    rc = ensure_ws(c, L.total); if (rc) return rc;
+    /* A context whose scratch already holds this grow (rg_ctx_reserve, or an earlier call) is not touched: no allocation, no
+       synchronisation inside the asynchronous path.  Only a context that has to grow anyway tries for the optional tail too. */
+    if (c->ws_bytes < L.total) {
+        if (c->may_grow) ensure_ws(c, L.total_with_planes, false);
+        rc = ensure_ws(c, L.total); if (rc) return rc;
+    }
     cudaStream_t st = (cudaStream_t)stream;
     return nz == 1 ? launch_label<Cfg2D>(c, L, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, st)
                    : launch_label<Cfg3D>(c, L, d_image, nx, ny, nz, lo_ext, hi_ext, d_seeds, nseeds, threshold, d_mask, st);
@@ -788,7 +818,9 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
     if (!c->last_counters) { if (stats) memset(stats, 0, 16); return RG_OK; }
     CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
     CK(cudaStreamSynchronize(c->last_stream));
-    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX]; stats[3] = c->h_status[CTR_NFLAGGED]; }
+    /* stats[2]: tiles the walkers did not get through = labelled by the dense path + handed to the full pass */
+    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX] + c->h_status[CTR_NDENSE]; stats[3] = c->h_status[CTR_NFLAGGED]; }
+    c->last_full_tiles = c->h_status[CTR_NCOMPLEX];
     if (c->h_status[CTR_STATUS]) {
         if (c->h_status[CTR_STATUS] & ST_NODE_OVERFLOW)
             snprintf(g_err, sizeof g_err, "out of node ids (status=0x%x): this input needs more nodes per tile than the workspace holds "
@@ -936,9 +968,10 @@ extern "C" int rg_grow_region_2d(unsigned char *image, int width, int height, un
 #define RG_NOALLOC_MAX_SEEDS 2048
 static __device__ __align__(256) unsigned char g_noalloc_scratch[RG_NOALLOC_SCRATCH_BYTES];
 /* `g_noalloc_scratch` names a device object; in host code it is only a handle.  The address the kernels
-   need is looked up once per device, with that device current, and kept here. */
+   need is looked up once per device, with that device current, and kept here (all of it under g_mu). */
 static void *g_noalloc_addr[64];
 static bool g_noalloc_attr[64];
+static uint32_t *g_noalloc_counters[64];     /* where the last call on the device keeps its counters / status word */
 
 extern "C" int64_t rg_noalloc_scratch_bytes(void) { return (int64_t)RG_NOALLOC_SCRATCH_BYTES; }
 
@@ -949,7 +982,9 @@ extern "C" int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_
         return fail(RG_ERR_ARG, "bad argument");
     if (nseeds > RG_NOALLOC_MAX_SEEDS)
         return fail(RG_ERR_TOO_LARGE, "rg_grow_device_noalloc takes at most 2048 seeds (larger lists need the sorting scratch of rg_grow_device)");
-    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L);
+    /* always the worst-case layout: RG_NODE_BUDGET (a tuning aid of the context path) must not squeeze a larger volume into
+       the fixed array with average-case node space */
+    Layout L; int rc = layout_for(nx, ny, nz, nseeds, L, false);
     if (rc) return rc;
     if (L.total > (size_t)RG_NOALLOC_SCRATCH_BYTES) {
         snprintf(g_err, sizeof g_err, "rg_grow_device_noalloc: this size needs %zu bytes of scratch but the built-in scratch holds %u "
@@ -959,6 +994,8 @@ extern "C" int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return fail(RG_ERR_ARG, "device index");
+    rg_ctx view;                                            /* a view of the built-in scratch; owns nothing */
+    memset(&view, 0, sizeof view);
     {
         std::lock_guard<std::mutex> lk(g_mu);
         if (!g_noalloc_addr[dev]) {                         /* first call on this device */
@@ -967,14 +1004,38 @@ extern "C" int rg_grow_device_noalloc(const uint8_t *d_image, int64_t nx, int64_
             if (!p) return fail(RG_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
             g_noalloc_addr[dev] = p;
         }
+        view.ws = g_noalloc_addr[dev];
+        view.attr_set = g_noalloc_attr[dev];
     }
-    rg_ctx view;                                            /* a view of the built-in scratch; owns nothing */
-    memset(&view, 0, sizeof view);
     view.device = dev;
-    view.ws = g_noalloc_addr[dev];
     view.ws_bytes = RG_NOALLOC_SCRATCH_BYTES;
-    view.attr_set = g_noalloc_attr[dev];
+    view.worst_case_layout = true;                          /* may_grow stays false: ensure_ws can only refuse */
     rc = grow_device_impl(&view, d_image, nx, ny, nz, 0, 0, d_seeds_xyz, nseeds, threshold, d_mask, stream);
-    g_noalloc_attr[dev] = view.attr_set;
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        g_noalloc_attr[dev] = g_noalloc_attr[dev] || view.attr_set;
+        if (rc == RG_OK) g_noalloc_counters[dev] = view.last_counters;
+    }
     return rc;
+}
+
+/* The engine's self-check of the last rg_grow_device_noalloc on the current device (the context path reads the same
+   words with rg_ctx_status).  Waits for `stream`, copies 32 bytes into a local array -- no allocation here either. */
+extern "C" int rg_noalloc_status(uint32_t stats[4], void *stream)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(RG_ERR_ARG, "device index");
+    uint32_t *src;
+    { std::lock_guard<std::mutex> lk(g_mu); src = g_noalloc_counters[dev]; }
+    if (!src) { if (stats) memset(stats, 0, 16); return RG_OK; }
+    uint32_t h[CTR_WORDS];
+    CK(cudaMemcpyAsync(h, src, sizeof h, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (stats) { stats[0] = h[CTR_NODES]; stats[1] = h[CTR_STATUS]; stats[2] = h[CTR_NCOMPLEX] + h[CTR_NDENSE]; stats[3] = h[CTR_NFLAGGED]; }
+    if (h[CTR_STATUS]) {
+        snprintf(g_err, sizeof g_err, "engine self-check failed on the no-allocation path: status=0x%x mismatching faces=%u", h[CTR_STATUS], h[CTR_FACE_MISMATCH]);
+        return RG_ERR_INTERNAL;
+    }
+    return RG_OK;
 }

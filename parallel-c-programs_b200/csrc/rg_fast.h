@@ -24,6 +24,7 @@
  */
 #pragma once
 #include "rg_core.h"
+#include "rg_dense.h"
 
 namespace rg {
 
@@ -37,7 +38,10 @@ static_assert((int)HASH_N == (int)FAST_NODE_SLOTS, "one node slot per hash slot"
 
 template <class C>
 struct alignas(128) FastSmem {
-    uint8_t img[C::IMG_BYTES];
+    union alignas(128) U {
+        uint8_t img[C::IMG_BYTES];                /* the staged tile */
+        DenseSmem<C> d;                           /* ... and, once its link words are in registers, the state of the dense labelling path (rg_dense.h) */
+    } u;
     uint64_t mbar;
     /* Storage shared over time.  The cross-tile edge words and their prefix sums are dead once the edge list exists and the
        list of the longer walks takes their place; that list and the x = TX halo column (lean layout: one byte per (y, z),
@@ -145,17 +149,6 @@ RG_FN bool walk_component(const uint8_t *img, int vx, int vy, int vz, uint32_t t
     return true;
 }
 
-/* voxel (tile-local linear index) on this side of cross-tile edge `b` of face word (f, idx) */
-template <class C>
-RG_FN uint32_t face_voxel(int f, int idx, int b, int vy, int vz)
-{
-    int x, y, z;
-    if (f < 2) { int bi = idx * 32 + b; z = bi / C::TY; y = bi % C::TY; x = (f == F_XP) ? C::TX - 1 : 0; }
-    else if (f < 4) { z = idx / C::WX; x = (idx % C::WX) * 32 + b; y = (f == F_YP) ? vy - 1 : 0; }
-    else { y = idx / C::WX; x = (idx % C::WX) * 32 + b; z = (f == F_ZP) ? vz - 1 : 0; }
-    return (uint32_t)((z * C::TY + y) * C::TX + x);
-}
-
 /* cross-tile edge masks of the six faces, from the staged bytes (the same words build_edges<FACES>
  * produces, without touching the interior) */
 template <class C, class Exec>
@@ -234,11 +227,12 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     const int vy = (int)((P.ny - y0) < C::TY ? (P.ny - y0) : C::TY);
     const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
 
-    if (!ex.template tma_tile<C>(P, s.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.img, x0, y0, z0, true);   /* copies are in flight from here */
+    if (!ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.img, x0, y0, z0, true);   /* copies are in flight from here */
     if (P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);          /* fire-and-forget stores: they fill the load's latency */
     ex.pfor(C::FW_TOTAL, [&](int i) { s.v.e.u.f.fmask[i] = 0; });
     ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
-    if (!C::XR) {
+    auto load_xr = [&]() {
+        if (C::XR) return;
         /* lean layout: the x = TX column is not in the staged box; one byte per (y, z) straight from the image (the
            neighbouring tile's CTA reads the same lines, so these come from L2) */
         const bool has_col = x0 + C::TX < P.nx;
@@ -246,7 +240,8 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             const int y = q % C::TY, z = q / C::TY;
             s.v.e.xr[q] = (has_col && y < vy && z < vz) ? P.image[((z0 + z) * P.ny + (y0 + y)) * P.nx + x0 + C::TX] : (uint8_t)0;
         });
-    }
+    };
+    load_xr();
     ex.pfor(HASH_N / 32, [&](int i) { s.seedtab[i] = 0; });
     if (ex.tid() == 0) {
         uint32_t lo, hi; seed_range(P, tile, lo, hi);
@@ -258,21 +253,21 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     /* a tile whose own voxels are all equal is one component with representative 0 (solid interiors) */
     bool uniform = false;
     if (P.fast16 && P.tmode >= 1) {
-        const uint32_t pat = (uint32_t)s.img[img_off<C>(0, 0, 0)] * 0x01010101u;
-        u32x4 q0 = ld128(&s.img[img_off<C>(0, 0, 0)]);
+        const uint32_t pat = (uint32_t)s.u.img[img_off<C>(0, 0, 0)] * 0x01010101u;
+        u32x4 q0 = ld128(&s.u.img[img_off<C>(0, 0, 0)]);
         /* the first 16 voxels decide for almost every tile; all threads read the same bytes, so this branch is uniform */
         if (vx >= 16 && ((q0.x ^ pat) | (q0.y ^ pat) | (q0.z ^ pat) | (q0.w ^ pat)) == 0u) {
             bool differs = false;
             ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
                 int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
                 if (y >= vy || z >= vz || 16 * c >= vx) return;
-                u32x4 q = ld128(&s.img[img_off<C>(16 * c, y, z)]);
+                u32x4 q = ld128(&s.u.img[img_off<C>(16 * c, y, z)]);
                 if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) differs = true;
             });
             uniform = !ex.sync_or(differs);
         }
     }
-    build_face_masks<C>(ex, P, s.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
+    build_face_masks<C>(ex, P, s.u.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
     ex.sync();
     if (P.debug_stop == 3) return;
     const uint32_t etot = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.v.e.u.f.fmask[i]); }, s.v.e.u.f.fprefix, s.scan_scratch);
@@ -289,7 +284,11 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         nnodes = (etot || seeded) ? 1u : 0u;
         if (ex.tid() == 0 && nnodes) { P.nparent[base] = seeded ? 0u : base; P.nrep[base] = 0; }
     } else {
-        if (etot > (uint32_t)FAST_ENT_MAX) { fast_give_up<C>(ex, P, tile); return; }     /* same total in every thread */
+        if (etot > (uint32_t)FAST_ENT_MAX || P.force_dense) {                            /* same total in every thread */
+            /* too many cross-tile edges for the walkers: label the tile from the staged bytes (rg_dense.h) */
+            if (!tile_label_dense<C>(ex, P, tile, s, x0, vy, vz)) fast_give_up<C>(ex, P, tile);
+            return;
+        }
         /* start voxel of every cross-tile edge, in list order ... */
         ex.pfor(C::FW_TOTAL, [&](int fw) {
             uint32_t m = s.v.e.u.f.fmask[fw];
@@ -304,7 +303,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
            own component; the others go to a compact list so that the longer walks fill whole warps. */
         ex.pfor((int)etot, [&](int e) {
             const uint32_t v = s.ent_root[e];
-            if (neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v)) s.v.e.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
+            if (neighbour_mask<C>(s.u.img, vx, vy, vz, P.thr, v)) s.v.e.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
             else s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, v);
         });
         {
@@ -312,7 +311,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             ex.pfor(hi - lo, [&](int i) {
                 const uint32_t v = (uint32_t)(P.seed_keys[lo + i] & 0xFFFFu);
                 WalkQ wq; int n; uint32_t root;
-                if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+                if (!walk_component<C>(s.u.img, vx, vy, vz, P.thr, v, neighbour_mask<C>(s.u.img, vx, vy, vz, P.thr, v), wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
                 const uint32_t slot = hash_slot(s.tab, s.scal, root);
                 atomic_or(&s.seedtab[slot >> 5], 1u << (slot & 31));
             });
@@ -323,18 +322,36 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             const int e = s.v.e.u.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
-            const uint32_t nb0 = neighbour_mask<C>(s.img, vx, vy, vz, P.thr, v);
+            const uint32_t nb0 = neighbour_mask<C>(s.u.img, vx, vy, vz, P.thr, v);
             if (P.debug_stop == 61) { s.ent_root[e] = (uint16_t)nb0; return; }
-            if (!walk_component<C>(s.img, vx, vy, vz, P.thr, v, nb0, wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
+            if (!walk_component<C>(s.u.img, vx, vy, vz, P.thr, v, nb0, wq, n, root)) { s.scal[SC_COMPLEX] = 1; return; }
             if (P.debug_stop == 62) { s.ent_root[e] = (uint16_t)root; return; }
             s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, root);
         });
         ex.sync();
         if (P.debug_stop == 7 || P.debug_stop == 61 || P.debug_stop == 62) return;
-        if (s.scal[SC_COMPLEX]) { fast_give_up<C>(ex, P, tile); return; }
-        /* dense ids in slot order, then face lists and nodes go out in one sweep */
-        nnodes = ex.scan16(HASH_N, [&](int i) { return s.tab[i] ? 1u : 0u; }, s.v.slotid, s.scan_scratch);
-        if (nnodes > (uint32_t)HASH_MAX_KEYS) { fast_give_up<C>(ex, P, tile); return; }
+        /* a walk that did not end, or more components than node slots: the dense path labels the tile from the bytes
+           that are still staged (the walkers have used the storage of the edge masks: rebuild them first) */
+        bool dense = s.scal[SC_COMPLEX] != 0;
+        nnodes = 0;
+        if (!dense) {
+            /* dense ids in slot order (this overwrites the halo column and the edge masks too: rebuilt below if it comes to that) */
+            nnodes = ex.scan16(HASH_N, [&](int i) { return s.tab[i] ? 1u : 0u; }, s.v.slotid, s.scan_scratch);
+            dense = nnodes > (uint32_t)HASH_MAX_KEYS;
+        }
+        if (dense) {
+            ex.pfor(C::FW_TOTAL, [&](int i) { s.v.e.u.f.fmask[i] = 0; });
+            load_xr();
+            ex.sync();
+            build_face_masks<C>(ex, P, s.u.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
+            ex.sync();
+            const uint32_t etot2 = ex.scan16(C::FW_TOTAL, [&](int i) { return (uint32_t)popc(s.v.e.u.f.fmask[i]); }, s.v.e.u.f.fprefix, s.scan_scratch);
+            if (ex.tid() == 0) s.v.e.u.f.fprefix[C::FW_TOTAL] = (uint16_t)etot2;
+            ex.sync();
+            if (!tile_label_dense<C>(ex, P, tile, s, x0, vy, vz)) fast_give_up<C>(ex, P, tile);
+            return;
+        }
+        /* face lists and nodes go out in one sweep */
         ex.pfor((int)etot, [&](int e) { ent[e] = s.v.slotid[s.ent_root[e]]; });
         ex.pfor(HASH_N, [&](int slot) {
             const uint32_t cur = s.tab[slot];
@@ -359,7 +376,7 @@ RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
 {
     const uint32_t n = P.counters[CTR_NCOMPLEX];
     for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
-        tile_pass_a<C>(ex, P, P.complex_list[i], s, i);             /* list position = slot of the saved link planes */
+        tile_pass_a<C>(ex, P, P.complex_list[i], s);
         ex.sync();
     }
 }

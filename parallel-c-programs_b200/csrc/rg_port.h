@@ -34,12 +34,8 @@ struct u32x4 { uint32_t x, y, z, w; };
 RG_FN int popc(uint32_t x) { return __popc(x); }
 RG_FN int clz(uint32_t x) { return __clz((int)x); }
 RG_FN int ffs1(uint32_t x) { return __ffs((int)x); }          /* 1-based, 0 if x == 0 */
-/* per-byte |a-b| < t  ->  4-bit nibble (bit j <-> byte j); t4 = t replicated into 4 bytes, 1 <= t <= 255 */
-RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
-{
-    uint32_t m = __vcmpltu4(__vabsdiffu4(a, b), t4);          /* 0xFF per similar byte */
-    return ((m & 0x01010101u) * 0x01020408u) >> 24;           /* gather the 4 flags into bits 0..3 */
-}
+RG_FN uint32_t vabsdiff4(uint32_t a, uint32_t b) { return __vabsdiffu4(a, b); }                 /* one VABSDIFF4 */
+RG_FN uint32_t funnel_l(uint32_t lo, uint32_t hi, int n) { return __funnelshift_l(lo, hi, n); }   /* (hi:lo << n) >> 32 */
 RG_FN uint32_t absdiff(uint32_t a, uint32_t b) { return __sad((int)a, (int)b, 0u); }
 RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { return atomicOr(p, v); }
 RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { return atomicAdd(p, v); }
@@ -88,15 +84,16 @@ RG_FN void cp_async_wait_all() {}
 RG_FN int popc(uint32_t x) { return __builtin_popcount(x); }
 RG_FN int clz(uint32_t x) { return x ? __builtin_clz(x) : 32; }
 RG_FN int ffs1(uint32_t x) { return __builtin_ffs((int)x); }
-RG_FN uint32_t edge4(uint32_t a, uint32_t b, uint32_t t4)
+RG_FN uint32_t vabsdiff4(uint32_t a, uint32_t b)
 {
-    uint32_t r = 0; int t = (int)(t4 & 0xFF);
+    uint32_t r = 0;
     for (int j = 0; j < 4; j++) {
-        int x = (a >> (8 * j)) & 0xFF, y = (b >> (8 * j)) & 0xFF, d = x > y ? x - y : y - x;
-        if (d < t) r |= 1u << j;
+        uint32_t x = (a >> (8 * j)) & 0xFF, y = (b >> (8 * j)) & 0xFF;
+        r |= (x > y ? x - y : y - x) << (8 * j);
     }
     return r;
 }
+RG_FN uint32_t funnel_l(uint32_t lo, uint32_t hi, int n) { return (uint32_t)(((((uint64_t)hi << 32) | lo) << n) >> 32); }
 RG_FN uint32_t absdiff(uint32_t a, uint32_t b) { return a > b ? a - b : b - a; }
 RG_FN uint32_t atomic_or(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o | v; return o; }
 RG_FN uint32_t atomic_add(uint32_t *p, uint32_t v) { uint32_t o = *p; *p = o + v; return o; }
@@ -114,6 +111,32 @@ RG_FN void st128(void *p, u32x4 v) { check16(p); memcpy(p, &v, 16); }
 RG_FN u32x4 ld128_stream(const void *p) { return ld128(p); }
 RG_FN void st128_stream(void *p, u32x4 v) { st128(p, v); }
 #endif
+
+/* Per-byte |a-b| < t for four voxels at once, as a 4-bit nibble (bit j <-> byte j).
+ *
+ * The SIMD-in-a-register compare of the toolkit (__vcmpltu4) is emulated with ~8 integer instructions on
+ * sm_100a; this form needs 4 after the VABSDIFF4.  With d = |a-b| per byte, H = 0x80 in every byte and
+ * t in 1..255:   u = (d | H) - c,  c = t (t <= 128) or t - 128 (t > 128) in every byte.
+ * Bit 7 of every byte of d | H is set and c <= 128, so no byte borrows from its neighbour, and bit 7 of
+ * u says "the low 7 bits of d are >= c".  For t <= 128:  d >= t  <=>  bit 7 of (u | d)  (a d with its own
+ * bit 7 set is >= 128 >= t);  for t > 128:  d >= t  <=>  bit 7 of (u & d).  `sel` = all ones / zero picks
+ * the two with one three-input logic operation.  The four flags (bits 7, 15, 23, 31 of `lt`) are gathered
+ * into bits 28..31 by one multiplication: 2^21 + 2^14 + 2^7 + 1 moves them there and no two partial
+ * products share a bit, so nothing carries. */
+struct ByteCmp { uint32_t c, sel; };
+RG_FN ByteCmp byte_cmp_for(uint32_t t)                         /* 1 <= t <= 255 */
+{
+    ByteCmp k; k.c = (t <= 128u ? t : t - 128u) * 0x01010101u; k.sel = t <= 128u ? 0xFFFFFFFFu : 0u;
+    return k;
+}
+RG_FN uint32_t lt4_top_nibble(uint32_t a, uint32_t b, ByteCmp k)   /* result in bits 28..31, garbage below */
+{
+    const uint32_t H = 0x80808080u;
+    const uint32_t d = vabsdiff4(a, b);
+    const uint32_t u = (d | H) - k.c;
+    const uint32_t ge = (u & d) | ((u | d) & k.sel);
+    return (~ge & H) * 0x00204081u;
+}
 
 /* 4 mask bits -> 4 bytes of 0/1 */
 RG_FN uint32_t expand4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }

@@ -38,6 +38,7 @@ SIGNATURES = {
     "rg_grow_device": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp, _vp]),
     "rg_grow_device_noalloc": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp, _vp]),
     "rg_noalloc_scratch_bytes": (_i64, []),
+    "rg_noalloc_status": (_i32, [_vp, _vp]),
     "rg_ctx_status": (_i32, [_vp, _vp]),
     "rg_ctx_profile": (_i32, [_vp, _i32]),
     "rg_ctx_profile_read": (_i32, [_vp, _vp]),

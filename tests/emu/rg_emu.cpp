@@ -20,8 +20,10 @@
 using namespace rg;
 
 struct HostExec {
+    static constexpr int NTHREADS = 1;
     int tid() const { return 0; }
     template <class F> void pfor(int n, F f) { for (int i = 0; i < n; i++) f(i); }
+    template <class F> void pfor_k(int n, F f) { for (int i = 0; i < n; i++) f(i, i); }
     template <class F> void gpfor(int64_t n, F f) { for (int64_t i = 0; i < n; i++) f(i); }
     template <class Pr, class Bo> void wfor(uint32_t n, Pr pred, Bo body)
     {
@@ -54,6 +56,11 @@ struct HostExec {
 
 static int g_force_full = 0;
 static int g_no_planes = 0;      /* 1: label every tile with the full pass (fast pass off) */
+static int g_force_dense = 0;    /* 1: every non-uniform tile takes the dense path of the fast pass */
+static uint32_t g_last_dense = 0, g_last_full = 0;
+extern "C" void emu_force_dense(int v) { g_force_dense = v; }
+extern "C" uint32_t emu_last_dense(void) { return g_last_dense; }
+extern "C" uint32_t emu_last_full(void) { return g_last_full; }
 extern "C" void emu_force_full(int v) { g_force_full = v; }
 extern "C" void emu_no_planes(int v) { g_no_planes = v; }
 
@@ -73,6 +80,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.lo_ext = zlo; P.hi_ext = zhi;
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
     P.mask_prezeroed = g_force_full ? 0 : 1;
+    P.force_dense = g_force_dense;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
     size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
     size_t cap = 1 + ntiles * ((size_t)C::ENT_MAX + FAST_NODE_SLOTS) + (size_t)nseeds;
@@ -126,7 +134,8 @@ static int emu_grow_t(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, 
     emu_label<C>(E);
     emu_finish<C>(E);
     uint32_t real_nodes = 0; for (const TileRec &r : E.rec) real_nodes += r.nnodes;
-    if (stats) { stats[0] = real_nodes; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX]; stats[3] = (uint32_t)E.rec.size(); }
+    if (stats) { stats[0] = real_nodes; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX] + E.counters[CTR_NDENSE]; stats[3] = (uint32_t)E.rec.size(); }
+    g_last_dense = E.counters[CTR_NDENSE]; g_last_full = E.counters[CTR_NCOMPLEX];
     return E.counters[CTR_STATUS] ? -4 : 0;
 }
 
@@ -318,7 +327,7 @@ extern "C" int rg_slab_resolve_packed(void *cv, uint32_t *xpar, uint32_t xpar_ca
 extern "C" int rg_ctx_status(void *cv, uint32_t *stats)
 {
     EmuCtx *c = (EmuCtx *)cv;
-    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX] + c->E.counters[CTR_NDENSE]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
     return c->E.counters[CTR_STATUS] ? -4 : 0;
 }
 extern "C" int rg_slab_finish(void *cv, void *)

@@ -251,3 +251,55 @@ def test_emu_random_stress(emu, oracle):
         if axis_len >= 2 * G:                                       # every logical rank needs two planes / rows
             got, _ = run_emu(emu, cfg, img, seeds, T, slabs=G)
             assert (got == want).all(), ("slabs", case, cfg, shape, levels, T, G)
+
+
+def test_emu_dense_path_labels_every_tile(emu, oracle):
+    """the dense path of the fast pass (rg_dense.h: link words, ranked runs, union-find on run ids) forced onto every
+    non-uniform tile: random grids in all emulator tile shapes, ragged sizes, 2-D and 3-D, multi-slab too"""
+    emu.emu_last_dense.restype = ctypes.c_uint32; emu.emu_last_full.restype = ctypes.c_uint32
+    rng = np.random.default_rng(77)
+    emu.emu_force_dense(1)
+    try:
+        for case in range(80):
+            cfg = int(rng.integers(0, 3))
+            if rng.random() < 0.3:
+                shape = (int(rng.integers(1, 150)), int(rng.integers(1, 300)))
+            else:
+                shape = (int(rng.integers(1, 20)), int(rng.integers(1, 40)), int(rng.integers(1, 140)))
+            levels = int(rng.choice([2, 3, 5, 12, 40]))
+            T = int(rng.choice([0, 1, 1, 2, 3, 17, 129, 200, 255, 256]))
+            img, seeds = rand_case(rng, shape, levels, int(rng.integers(0, 7)))
+            want = oracle.grow(img, seeds, T)
+            got, st = run_emu(emu, cfg, img, seeds, T)
+            assert (got == want).all(), (case, cfg, shape, levels, T)
+            assert emu.emu_last_full() == 0, (case, cfg, shape)
+            G = int(rng.integers(2, 4))
+            if cfg != 0 and shape[0] >= 2 * G:
+                got, _ = run_emu(emu, cfg, img, seeds, T, slabs=G)
+                assert (got == want).all(), ("slabs", case, cfg, shape, levels, T, G)
+        for kind, n in (("c3", 40), ("c4", 96), ("c1h", 64), ("c2", 256)):
+            img, seeds, T = oracle.synth(kind, n, 0x5EED0000)
+            for cfg in (0, 1):
+                got, _ = run_emu(emu, cfg, img, seeds, T)
+                assert (got == oracle.grow(img, seeds, T)).all(), (kind, cfg)
+                assert emu.emu_last_dense() > 0
+    finally:
+        emu.emu_force_dense(0)
+
+
+def test_emu_dense_path_overflow_goes_to_the_full_pass(emu, oracle):
+    """a product-size tile with more ranked runs than the dense path's parent table holds (every voxel its own run,
+    all of them linked in y) is handed to the full labelling pass; its neighbours stay on the dense path"""
+    emu.emu_last_dense.restype = ctypes.c_uint32; emu.emu_last_full.restype = ctypes.c_uint32
+    img = np.zeros((16, 64, 128), np.uint8)
+    img[:, :, :64] = (np.arange(64) % 2 * 100).astype(np.uint8)[None, None, :]      # columns 0/100: runs of one voxel, linked in y and z
+    img[:, :, 64:] = np.random.default_rng(3).integers(0, 12, size=(16, 64, 64))
+    seeds = [[0, 0, 0], [1, 5, 5], [100, 40, 3]]
+    want = oracle.grow(img, seeds, 1)
+    emu.emu_force_dense(1)
+    try:
+        got, st = run_emu(emu, 0, img, seeds, 1)
+    finally:
+        emu.emu_force_dense(0)
+    assert (got == want).all()
+    assert emu.emu_last_full() >= 1 and emu.emu_last_dense() >= 1, (emu.emu_last_full(), emu.emu_last_dense())
