@@ -11,6 +11,30 @@
 
 #include <stdint.h>
 
+/* The three on-disk header records of an 8-bit BMP, under the names and field names the reference's header
+ * exports (bmp.h:6-30), so that a caller that fills or inspects them keeps compiling.  The library's own reader
+ * and writer (csrc/bmp.c) do not use them -- they address the file by byte offset -- and neither do region.c,
+ * raycast.cu or raycast.c.  Sizes: 2, 12 and 40 bytes; a file is bmp_id, bmp_header, bmp_dib_header, palette, pixels. */
+struct bmp_id {                    /* the two magic bytes "BM" */
+    uint8_t magic1, magic2;
+};
+struct bmp_header {                /* file header after the magic: offsets 2..13 */
+    uint32_t file_size;
+    uint16_t creator1, creator2;   /* application-defined; the reference leaves them uninitialised, this library writes 0 */
+    uint32_t pixel_offset;         /* where the pixel payload starts (1078 for an 8-bit image with a 256-entry palette) */
+};
+struct bmp_dib_header {            /* BITMAPINFOHEADER: offsets 14..53 */
+    uint32_t header_size;          /* 40 */
+    int32_t  width, height;
+    uint16_t num_planes;           /* 1 */
+    uint16_t bit_pr_pixel;         /* 8 */
+    uint32_t compress_type;        /* 0 = uncompressed */
+    uint32_t data_size;            /* width * height */
+    int32_t  hres, vres;
+    uint32_t num_colors;           /* 256 */
+    uint32_t num_imp_colors;
+};
+
 #ifdef __cplusplus
 extern "C" {
 #endif

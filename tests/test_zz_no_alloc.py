@@ -1,9 +1,11 @@
 """rg_grow_device_noalloc: the grow for callers that may not allocate device memory while running
 (a host whose own pool owns the card, a latency-critical loop that cannot take cudaMalloc's device-wide
 synchronisation or a late out-of-memory error).  Its scratch is a fixed 64 MiB array inside the library
-instead of a context's workspace, so the only thing to check is that it computes exactly what the
-context-based entry point computes -- on two calls in a row, because the second call finds the first
-call's leftovers in the shared array -- and that it refuses sizes the array cannot hold.
+instead of a context's workspace, so the things to check are that it computes exactly what the
+context-based entry point computes (and what the CPU oracle computes) -- on two calls in a row, because the
+second call finds the first call's leftovers in the shared array --, that the amount of free device memory
+does not move across a call, that its self-check can be read (rg_noalloc_status), and that it refuses sizes
+the array cannot hold.
 
 Collected last on purpose (file name): a failure here cannot hide the results of the other tests."""
 import ctypes
@@ -33,7 +35,13 @@ def _noalloc(torch, lib, d_img, d_seeds, T):
     return out
 
 
-def test_noalloc_matches_context_entry_point_twice():
+def _status(torch, lib):
+    st = (ctypes.c_uint32 * 4)()
+    rc = lib.rg_noalloc_status(st, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    return rc, list(st)
+
+
+def test_noalloc_matches_context_entry_point_twice(oracle):
     torch, rgb200, lib = _setup()
     rng = np.random.default_rng(2024)
     ctx = rgb200.Context(0)
@@ -47,10 +55,21 @@ def test_noalloc_matches_context_entry_point_twice():
         d_img = torch.from_numpy(img).cuda(); d_seeds = torch.from_numpy(seeds).cuda()
         want = torch.empty_like(d_img)
         ctx.grow(d_img, d_seeds, T, want)                          # the existing, context-based entry point
-        got = _noalloc(torch, lib, d_img, d_seeds, T)
+        _noalloc(torch, lib, d_img, d_seeds, T)                    # (the very first call on a device looks up the array's address)
+        out = torch.full_like(d_img, 5)                            # the caller's output buffer exists before the measured call
         torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
+        nz, ny, nx = (1,) + tuple(d_img.shape) if d_img.dim() == 2 else tuple(d_img.shape)
+        rc = lib.rg_grow_device_noalloc(d_img.data_ptr(), nx, ny, nz, d_seeds.data_ptr(), len(seeds), T, out.data_ptr(),
+                                        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        assert rc == 0 and torch.cuda.mem_get_info()[0] == free_before      # the call took no device memory
+        got = out
         assert ctx.status()["status"] == 0
+        rc, st = _status(torch, lib)
+        assert rc == 0 and st[1] == 0 and st[0] > 0                # self-check of the no-allocation path: readable and clean
         assert torch.equal(got, want)                              # integer path: bit-exact
+        assert (got.cpu().numpy() == oracle.grow(img, seeds, T)).all()   # ... and equal to the CPU oracle, not just to the other CUDA path
         assert int(want.sum()) > 0
     # the first volume again: nothing of call 2 may leak into it
     d_img = torch.from_numpy(vol).cuda(); d_seeds = torch.from_numpy(cases[0][1]).cuda()
