@@ -370,8 +370,13 @@ def test_node_budget_overflow_is_reported(rg, oracle, monkeypatch):
     """volumes beyond ~17 Gvoxel (and RG_NODE_BUDGET runs) size the node space for an average number of nodes per
     tile; an input that needs more must fail loudly through the status word, and succeed again with room"""
     import torch
-    img, seeds, T = oracle.synth("c3", 128)                      # every tile goes through the full pass with hundreds of nodes
+    # every (x, y) column is its own component and runs through all planes: 2048 nodes per tile, twice the fixed block of
+    # node ids a tile owns, so every tile takes the rest from the shared space that RG_NODE_BUDGET shrinks
+    z, y, x = np.meshgrid(np.arange(64), np.arange(96), np.arange(192), indexing="ij")
+    img = (((x + 2 * y) % 5) * 40).astype(np.uint8)
+    seeds, T = np.array([[0, 0, 0], [100, 50, 63], [191, 95, 10]], np.int32), 1
     want = oracle.grow(img, seeds, T)
+    assert int(want.sum()) == 3 * 64
     d_img = torch.from_numpy(img).cuda(); d_seeds = torch.from_numpy(seeds).cuda(); out = torch.empty_like(d_img)
     monkeypatch.setenv("RG_NODE_BUDGET", "4")
     c1 = rg.Context(0)
