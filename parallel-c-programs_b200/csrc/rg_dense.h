@@ -176,28 +176,48 @@ RG_FN bool tile_label_dense(Exec &ex, const Params &P, uint32_t tile, S &s, int6
         st128(&d.parent[v], u32x4{ v | ((v + 1) << 16), (v + 2) | ((v + 3) << 16), (v + 4) | ((v + 5) << 16), (v + 6) | ((v + 7) << 16) });
     });
     ex.sync();
-    ex.pfor(C::NW, [&](int w) {
-        const uint32_t lsw = d.ls[w];
-        if (!lsw) return;                                    /* no ranked run: no link leaves this word */
-        const int wx = w % C::WX;
-        const uint32_t exw = d.ex[w], pre = prefix[w];
-        if (wx < C::WX - 1 && (exw >> 31))
-            unite16(d.parent, run_id(exw, lsw, pre, 31), (uint32_t)prefix[w + 1]);   /* bit 0 of the next word starts its first run */
-        uint32_t m = pey[w];
-        if (m) {
-            const int up = w + C::WX; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
-            uint32_t n = dedupe(m, exw, exu);
-            while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(d.parent, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
-        }
-        if (C::HZ) {
-            m = pez[w];
+    /* Order matters for speed, not for the result.  If every word united with its neighbours at once, the rows of a solid
+       (or of C3's background) would all hook under the row above in the same instant: chains as long as the tile is high,
+       which every later find walks.  A thread that works through SEG consecutive rows (then planes) finds the tree it has
+       just extended already flat, so chains grow by one per SEG rows instead of one per row. */
+    constexpr int SEG = 4;
+    constexpr int NYSEG = (C::TY + SEG - 1) / SEG, NZSEG = (C::TZ + SEG - 1) / SEG;
+    ex.pfor(C::WX * NYSEG * C::TZ, [&](int it) {
+        const int wx = it % C::WX, ys = (it / C::WX) % NYSEG, z = it / (C::WX * NYSEG);
+        for (int j = 0; j < SEG; j++) {
+            const int y = ys * SEG + j;
+            if (y >= C::TY) break;
+            const int w = (z * C::TY + y) * C::WX + wx;
+            const uint32_t lsw = d.ls[w];
+            if (!lsw) continue;                              /* no ranked run: no link leaves this word */
+            const uint32_t exw = d.ex[w], pre = prefix[w];
+            if (wx < C::WX - 1 && (exw >> 31))
+                unite16(d.parent, run_id(exw, lsw, pre, 31), (uint32_t)prefix[w + 1]);   /* bit 0 of the next word starts its first run */
+            const uint32_t m = pey[w];
             if (m) {
-                const int up = w + C::WX * C::TY; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
+                const int up = w + C::WX; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
                 uint32_t n = dedupe(m, exw, exu);
                 while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(d.parent, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
             }
         }
     });
+    if (C::HZ) {
+        ex.sync();
+        ex.pfor(C::WX * C::TY * NZSEG, [&](int it) {
+            const int r = it % (C::WX * C::TY), zs = it / (C::WX * C::TY);
+            for (int j = 0; j < SEG; j++) {
+                const int z = zs * SEG + j;
+                if (z >= C::TZ - 1) break;
+                const int w = z * C::WX * C::TY + r;
+                const uint32_t m = pez[w];
+                if (!m) continue;
+                const int up = w + C::WX * C::TY;
+                const uint32_t exw = d.ex[w], lsw = d.ls[w], pre = prefix[w], exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
+                uint32_t n = dedupe(m, exw, exu);
+                while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(d.parent, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
+            }
+        });
+    }
     ex.sync();
 
     /* 4. roots that own a cross-tile edge or a seed become nodes */
@@ -214,7 +234,7 @@ RG_FN bool tile_label_dense(Exec &ex, const Params &P, uint32_t tile, S &s, int6
         const uint32_t all = fmask[fw];
         uint32_t m = all & (0xFFu << q8);
         if (!m) return;
-        int f = 0; while (fw >= C::fw_off(f + 1)) f++;
+        const int f = (fw >= C::fw_off(1)) + (fw >= C::fw_off(2)) + (fw >= C::fw_off(3)) + (fw >= C::fw_off(4)) + (fw >= C::fw_off(5));
         const int idx = fw - C::fw_off(f);
         uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
         while (m) {

@@ -319,6 +319,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         ex.sync();
         if (P.debug_stop == 6) return;
         ex.pfor((int)s.scal[SC_NSLOW], [&](int i) {
+            if (ldv32(&s.scal[SC_COMPLEX])) return;                 /* a walk has overflowed already: the tile goes to the dense path, the rest is moot */
             const int e = s.v.e.u.slow[i];
             const uint32_t v = s.ent_root[e];
             WalkQ wq; int n; uint32_t root;
