@@ -97,6 +97,157 @@ RG_FN uint32_t run_id(uint32_t exw, uint32_t lsw, uint32_t pre, int bit)
     return pre + (uint32_t)popc(lsw & ((1u << sb) - 1u));
 }
 
+/* the rest of the dense path: union-find over `nruns` ranked runs on parents of type PT, nodes, face lists, tile record */
+template <class C, class PT, class S, class Exec>
+RG_FN void dense_label_runs(Exec &ex, const Params &P, uint32_t tile, S &s, PT *par, uint32_t nruns, int vy, int vz)
+{
+    typedef DenseCfg<C> D;
+    DenseSmem<C> &d = s.u.d;
+    uint32_t *const pey = d.eyz, *const pez = d.eyz + C::NW;
+    const uint32_t *fmask = s.v.e.u.f.fmask;
+    const uint16_t *fprefix = s.v.e.u.f.fprefix;
+    const uint16_t *prefix = reinterpret_cast<const uint16_t *>(s.tab);
+    const int slo = (int)s.scal[SC_SEED_LO], shi = (int)s.scal[SC_SEED_HI];
+    /* 3. union-find over the ranked runs */
+    if (sizeof(PT) == 2) ex.pfor((int)((nruns + 7u) / 8u), [&](int it) {
+        const uint32_t v = (uint32_t)it * 8;
+        st128(&par[v], u32x4{ v | ((v + 1) << 16), (v + 2) | ((v + 3) << 16), (v + 4) | ((v + 5) << 16), (v + 6) | ((v + 7) << 16) });
+    });
+    else ex.pfor((int)((nruns + 3u) / 4u), [&](int it) {
+        const uint32_t v = (uint32_t)it * 4;
+        st128(&par[v], u32x4{ v, v + 1, v + 2, v + 3 });
+    });
+    ex.sync();
+    /* Order matters for speed, not for the result.  If every word united with its neighbours at once, the rows of a solid
+       (or of C3's background) would all hook under the row above in the same instant: chains as long as the tile is high,
+       which every later find walks.  A thread that works through SEG consecutive rows (then planes) finds the tree it has
+       just extended already flat, so chains grow by one per SEG rows instead of one per row. */
+    constexpr int SEG = 4;
+    constexpr int NYSEG = (C::TY + SEG - 1) / SEG, NZSEG = (C::TZ + SEG - 1) / SEG;
+    ex.pfor(C::WX * NYSEG * C::TZ, [&](int it) {
+        const int wx = it % C::WX, ys = (it / C::WX) % NYSEG, z = it / (C::WX * NYSEG);
+        for (int j = 0; j < SEG; j++) {
+            const int y = ys * SEG + j;
+            if (y >= C::TY) break;
+            const int w = (z * C::TY + y) * C::WX + wx;
+            const uint32_t lsw = d.ls[w];
+            if (!lsw) continue;                              /* no ranked run: no link leaves this word */
+            const uint32_t exw = d.ex[w], pre = prefix[w];
+            if (wx < C::WX - 1 && (exw >> 31))
+                unite16(par, run_id(exw, lsw, pre, 31), (uint32_t)prefix[w + 1]);   /* bit 0 of the next word starts its first run */
+            const uint32_t m = pey[w];
+            if (m) {
+                const int up = w + C::WX; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
+                uint32_t n = dedupe(m, exw, exu);
+                while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(par, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
+            }
+        }
+    });
+    if (C::HZ) {
+        ex.sync();
+        ex.pfor(C::WX * C::TY * NZSEG, [&](int it) {
+            const int r = it % (C::WX * C::TY), zs = it / (C::WX * C::TY);
+            for (int j = 0; j < SEG; j++) {
+                const int z = zs * SEG + j;
+                if (z >= C::TZ - 1) break;
+                const int w = z * C::WX * C::TY + r;
+                const uint32_t m = pez[w];
+                if (!m) continue;
+                const int up = w + C::WX * C::TY;
+                const uint32_t exw = d.ex[w], lsw = d.ls[w], pre = prefix[w], exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
+                uint32_t n = dedupe(m, exw, exu);
+                while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(par, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
+            }
+        });
+    }
+    ex.sync();
+
+    /* 4. roots that own a cross-tile edge or a seed become nodes */
+    uint32_t *open = D::ALIAS_POST ? d.eyz : d.post_bits;
+    uint32_t *seeded = open + D::CAPW;
+    uint16_t *nprefix = D::ALIAS_POST ? reinterpret_cast<uint16_t *>(d.eyz + 2 * D::CAPW) : d.post_prefix;
+    const int idw = (int)((nruns + 31u) / 32u);
+    ex.pfor(idw, [&](int i) { open[i] = 0; seeded[i] = 0; });
+    ex.sync();
+    uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
+    /* a quarter of a face word per item: the root of each edge's run goes to the face list for now */
+    ex.pfor(4 * C::FW_TOTAL, [&](int it) {
+        const int fw = it >> 2, q8 = (it & 3) * 8;
+        const uint32_t all = fmask[fw];
+        uint32_t m = all & (0xFFu << q8);
+        if (!m) return;
+        const int f = (fw >= C::fw_off(1)) + (fw >= C::fw_off(2)) + (fw >= C::fw_off(3)) + (fw >= C::fw_off(4)) + (fw >= C::fw_off(5));
+        const int idx = fw - C::fw_off(f);
+        uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
+        while (m) {
+            const int b = ffs1(m) - 1; m &= m - 1;
+            const uint32_t v = face_voxel<C>(f, idx, b, vy, vz);
+            const int w = (int)(v >> 5);
+            const uint32_t r = find16(par, run_id(d.ex[w], d.ls[w], prefix[w], (int)(v & 31)));
+            atomic_or(&open[r >> 5], 1u << (r & 31));
+            ent[slot++] = (uint16_t)r;
+        }
+    });
+    ex.pfor(shi - slo, [&](int i) {
+        const uint32_t v = (uint32_t)(P.seed_keys[slo + i] & 0xFFFFu);
+        const int w = (int)(v >> 5);
+        const uint32_t r = find16(par, run_id(d.ex[w], d.ls[w], prefix[w], (int)(v & 31)));
+        atomic_or(&open[r >> 5], 1u << (r & 31));
+        atomic_or(&seeded[r >> 5], 1u << (r & 31));
+    });
+    ex.sync();
+    const uint32_t k = ex.scan16(idw, [&](int i) { return (uint32_t)popc(open[i]); }, nprefix, s.scan_scratch);
+    if (ex.tid() == 0) {
+        /* the tile's fixed block of node ids if it is enough (no global atomic), else ids from behind the blocks */
+        uint32_t base = 1u + tile * (uint32_t)FAST_NODE_SLOTS, bad = 0;
+        if (k > (uint32_t)FAST_NODE_SLOTS) {
+            base = atomic_add(&P.counters[CTR_NODES], k);
+            if (base + k > P.node_cap || base + k < base) { atomic_or(&P.counters[CTR_STATUS], ST_NODE_OVERFLOW); bad = 1; }
+        }
+        s.scal[SC_NODE_BASE] = base; s.scal[SC_OVERFLOW] = bad;
+    }
+    ex.sync();
+    const uint32_t base = s.scal[SC_NODE_BASE];
+    const bool ok = !s.scal[SC_OVERFLOW];
+    if (ok) {
+        ex.pfor(C::NW, [&](int w) {
+            uint32_t m = d.ls[w];
+            if (!m) return;
+            uint32_t id = prefix[w];
+            while (m) {
+                const int b = ffs1(m) - 1; m &= m - 1;
+                const uint32_t ow = open[id >> 5], bit = 1u << (id & 31);
+                if (ow & bit) {
+                    const uint32_t g = base + nprefix[id >> 5] + (uint32_t)popc(ow & (bit - 1u));
+                    P.nparent[g] = (seeded[id >> 5] & bit) ? 0u : g;       /* seeded components start hooked to node 0 */
+                    P.nrep[g] = (uint16_t)(w * 32 + b);
+                }
+                id++;
+            }
+        });
+        /* root ids -> node ids, each thread over the entries it wrote itself */
+        ex.pfor(4 * C::FW_TOTAL, [&](int it) {
+            const int fw = it >> 2, q8 = (it & 3) * 8;
+            const uint32_t all = fmask[fw];
+            const uint32_t m = all & (0xFFu << q8);
+            if (!m) return;
+            uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
+            for (int n = popc(m); n > 0; n--, slot++) {
+                const uint32_t r = ent[slot];
+                ent[slot] = (uint16_t)(nprefix[r >> 5] + (uint32_t)popc(open[r >> 5] & ((1u << (r & 31)) - 1u)));
+            }
+        });
+    }
+    if (ex.tid() == 0) {
+        TileRec rc;
+        rc.node_base = base; rc.nnodes = ok ? k : 0u;
+        for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)s.scal[SC_CNT0 + f] : (uint16_t)0;
+        rc.uniform = 0; rc.pad1 = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
+        P.rec[tile] = rc;
+        atomic_add(&P.counters[CTR_NDENSE], 1u);
+    }
+}
+
 /* S = FastSmem<C> (rg_fast.h).  On entry the tile is staged in s.u.img and the cross-tile edge masks, their
    prefix sums (s.v.e.u.f) and the face counts (s.scal[SC_CNT0..]) are those of this tile.  Returns false if the
    tile has more ranked runs than the table holds: the caller hands it to the full pass. */
@@ -107,7 +258,6 @@ RG_FN bool tile_label_dense(Exec &ex, const Params &P, uint32_t tile, S &s, int6
     DenseSmem<C> &d = s.u.d;
     uint32_t *const pey = d.eyz, *const pez = d.eyz + C::NW;
     const uint32_t *fmask = s.v.e.u.f.fmask;
-    const uint16_t *fprefix = s.v.e.u.f.fprefix;
     uint16_t *prefix = reinterpret_cast<uint16_t *>(s.tab);  /* ranked runs before word w (the hash table is not needed here) */
     static_assert(sizeof(s.tab) >= 2 * C::NW, "the run prefix sums live in the hash table's storage");
 
@@ -170,140 +320,11 @@ RG_FN bool tile_label_dense(Exec &ex, const Params &P, uint32_t tile, S &s, int6
     const uint32_t nruns = ex.scan16(C::NW, [&](int i) { return (uint32_t)popc(d.ls[i]); }, prefix, s.scan_scratch);
     if (nruns > (uint32_t)D::CAP) return false;               /* same total in every thread */
 
-    /* 3. union-find over the ranked runs */
-    ex.pfor((int)((nruns + 7u) / 8u), [&](int it) {
-        const uint32_t v = (uint32_t)it * 8;
-        st128(&d.parent[v], u32x4{ v | ((v + 1) << 16), (v + 2) | ((v + 3) << 16), (v + 4) | ((v + 5) << 16), (v + 6) | ((v + 7) << 16) });
-    });
-    ex.sync();
-    /* Order matters for speed, not for the result.  If every word united with its neighbours at once, the rows of a solid
-       (or of C3's background) would all hook under the row above in the same instant: chains as long as the tile is high,
-       which every later find walks.  A thread that works through SEG consecutive rows (then planes) finds the tree it has
-       just extended already flat, so chains grow by one per SEG rows instead of one per row. */
-    constexpr int SEG = 4;
-    constexpr int NYSEG = (C::TY + SEG - 1) / SEG, NZSEG = (C::TZ + SEG - 1) / SEG;
-    ex.pfor(C::WX * NYSEG * C::TZ, [&](int it) {
-        const int wx = it % C::WX, ys = (it / C::WX) % NYSEG, z = it / (C::WX * NYSEG);
-        for (int j = 0; j < SEG; j++) {
-            const int y = ys * SEG + j;
-            if (y >= C::TY) break;
-            const int w = (z * C::TY + y) * C::WX + wx;
-            const uint32_t lsw = d.ls[w];
-            if (!lsw) continue;                              /* no ranked run: no link leaves this word */
-            const uint32_t exw = d.ex[w], pre = prefix[w];
-            if (wx < C::WX - 1 && (exw >> 31))
-                unite16(d.parent, run_id(exw, lsw, pre, 31), (uint32_t)prefix[w + 1]);   /* bit 0 of the next word starts its first run */
-            const uint32_t m = pey[w];
-            if (m) {
-                const int up = w + C::WX; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
-                uint32_t n = dedupe(m, exw, exu);
-                while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(d.parent, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
-            }
-        }
-    });
-    if (C::HZ) {
-        ex.sync();
-        ex.pfor(C::WX * C::TY * NZSEG, [&](int it) {
-            const int r = it % (C::WX * C::TY), zs = it / (C::WX * C::TY);
-            for (int j = 0; j < SEG; j++) {
-                const int z = zs * SEG + j;
-                if (z >= C::TZ - 1) break;
-                const int w = z * C::WX * C::TY + r;
-                const uint32_t m = pez[w];
-                if (!m) continue;
-                const int up = w + C::WX * C::TY;
-                const uint32_t exw = d.ex[w], lsw = d.ls[w], pre = prefix[w], exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
-                uint32_t n = dedupe(m, exw, exu);
-                while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(d.parent, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
-            }
-        });
-    }
-    ex.sync();
-
-    /* 4. roots that own a cross-tile edge or a seed become nodes */
-    uint32_t *open = D::ALIAS_POST ? d.eyz : d.post_bits;
-    uint32_t *seeded = open + D::CAPW;
-    uint16_t *nprefix = D::ALIAS_POST ? reinterpret_cast<uint16_t *>(d.eyz + 2 * D::CAPW) : d.post_prefix;
-    const int idw = (int)((nruns + 31u) / 32u);
-    ex.pfor(idw, [&](int i) { open[i] = 0; seeded[i] = 0; });
-    ex.sync();
-    uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
-    /* a quarter of a face word per item: the root of each edge's run goes to the face list for now */
-    ex.pfor(4 * C::FW_TOTAL, [&](int it) {
-        const int fw = it >> 2, q8 = (it & 3) * 8;
-        const uint32_t all = fmask[fw];
-        uint32_t m = all & (0xFFu << q8);
-        if (!m) return;
-        const int f = (fw >= C::fw_off(1)) + (fw >= C::fw_off(2)) + (fw >= C::fw_off(3)) + (fw >= C::fw_off(4)) + (fw >= C::fw_off(5));
-        const int idx = fw - C::fw_off(f);
-        uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
-        while (m) {
-            const int b = ffs1(m) - 1; m &= m - 1;
-            const uint32_t v = face_voxel<C>(f, idx, b, vy, vz);
-            const int w = (int)(v >> 5);
-            const uint32_t r = find16(d.parent, run_id(d.ex[w], d.ls[w], prefix[w], (int)(v & 31)));
-            atomic_or(&open[r >> 5], 1u << (r & 31));
-            ent[slot++] = (uint16_t)r;
-        }
-    });
-    ex.pfor(shi - slo, [&](int i) {
-        const uint32_t v = (uint32_t)(P.seed_keys[slo + i] & 0xFFFFu);
-        const int w = (int)(v >> 5);
-        const uint32_t r = find16(d.parent, run_id(d.ex[w], d.ls[w], prefix[w], (int)(v & 31)));
-        atomic_or(&open[r >> 5], 1u << (r & 31));
-        atomic_or(&seeded[r >> 5], 1u << (r & 31));
-    });
-    ex.sync();
-    const uint32_t k = ex.scan16(idw, [&](int i) { return (uint32_t)popc(open[i]); }, nprefix, s.scan_scratch);
-    if (ex.tid() == 0) {
-        /* the tile's fixed block of node ids if it is enough (no global atomic), else ids from behind the blocks */
-        uint32_t base = 1u + tile * (uint32_t)FAST_NODE_SLOTS, bad = 0;
-        if (k > (uint32_t)FAST_NODE_SLOTS) {
-            base = atomic_add(&P.counters[CTR_NODES], k);
-            if (base + k > P.node_cap || base + k < base) { atomic_or(&P.counters[CTR_STATUS], ST_NODE_OVERFLOW); bad = 1; }
-        }
-        s.scal[SC_NODE_BASE] = base; s.scal[SC_OVERFLOW] = bad;
-    }
-    ex.sync();
-    const uint32_t base = s.scal[SC_NODE_BASE];
-    const bool ok = !s.scal[SC_OVERFLOW];
-    if (ok) {
-        ex.pfor(C::NW, [&](int w) {
-            uint32_t m = d.ls[w];
-            if (!m) return;
-            uint32_t id = prefix[w];
-            while (m) {
-                const int b = ffs1(m) - 1; m &= m - 1;
-                const uint32_t ow = open[id >> 5], bit = 1u << (id & 31);
-                if (ow & bit) {
-                    const uint32_t g = base + nprefix[id >> 5] + (uint32_t)popc(ow & (bit - 1u));
-                    P.nparent[g] = (seeded[id >> 5] & bit) ? 0u : g;       /* seeded components start hooked to node 0 */
-                    P.nrep[g] = (uint16_t)(w * 32 + b);
-                }
-                id++;
-            }
-        });
-        /* root ids -> node ids, each thread over the entries it wrote itself */
-        ex.pfor(4 * C::FW_TOTAL, [&](int it) {
-            const int fw = it >> 2, q8 = (it & 3) * 8;
-            const uint32_t all = fmask[fw];
-            const uint32_t m = all & (0xFFu << q8);
-            if (!m) return;
-            uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
-            for (int n = popc(m); n > 0; n--, slot++) {
-                const uint32_t r = ent[slot];
-                ent[slot] = (uint16_t)(nprefix[r >> 5] + (uint32_t)popc(open[r >> 5] & ((1u << (r & 31)) - 1u)));
-            }
-        });
-    }
-    if (ex.tid() == 0) {
-        TileRec rc;
-        rc.node_base = base; rc.nnodes = ok ? k : 0u;
-        for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)s.scal[SC_CNT0 + f] : (uint16_t)0;
-        rc.uniform = 0; rc.pad1 = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
-        P.rec[tile] = rc;
-        atomic_add(&P.counters[CTR_NDENSE], 1u);
-    }
+    /* 3./4. in dense_label_runs.  Up to CAP / 2 runs -- the usual case -- the parents are 32-bit words: shared-memory
+       compare-and-swap is native at that width, while the 16-bit form is a retry loop on the enclosing word in which
+       neighbouring runs disturb each other */
+    if (nruns <= (uint32_t)D::CAP / 2) dense_label_runs<C>(ex, P, tile, s, reinterpret_cast<uint32_t *>(d.parent), nruns, vy, vz);
+    else dense_label_runs<C>(ex, P, tile, s, d.parent, nruns, vy, vz);
     return true;
 }
 

@@ -30,6 +30,41 @@ struct DevExec {
     uint32_t phase = 0;                     /* parity of the next mbarrier completion */
     bool tma_pending = false;
 
+    const CUtensorMap *tmap_mask = nullptr; /* mask descriptor for the bulk stores that clear a tile (fast labelling pass) */
+    bool store_pending = false;
+    /* barrier after generic-proxy writes to shared memory that the copy engine is going to read */
+    __device__ __forceinline__ void sync_async_smem()
+    {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+    }
+    /* Clear this tile's part of the mask with bulk tensor stores from `zeros` (shared memory, all zero, `bytes` long):
+       boxes of TX x BR x BZ bytes, one instruction each, issued by one thread; the hardware clips them at the volume's
+       border.  A box may reach into the next tile's rows (images: 126-row tiles, 32-row boxes) -- harmless, every CTA of
+       this kernel writes nothing but zeros to the mask.  The shared-memory source must stay zero until store_wait(). */
+    template <class C>
+    __device__ __forceinline__ bool tma_clear_tile(const Params &P, const void *zeros, int bytes, int64_t x0, int64_t y0, int64_t z0)
+    {
+        if (!P.use_tma || !tmap_mask) return false;
+        constexpr int BR = C::TY < 32 ? C::TY : 32;
+        const int BZ = bytes / (C::TX * BR) < C::TZ ? bytes / (C::TX * BR) : C::TZ;
+        store_pending = true;
+        if (threadIdx.x == 0) {
+            const uint32_t src = smem_u32(zeros);
+            for (int z = 0; z < C::TZ; z += BZ)
+                for (int y = 0; y < C::TY; y += BR)
+                    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+                                 :: "l"((uint64_t)tmap_mask), "r"(src), "r"((int)x0), "r"((int)y0 + y), "r"((int)z0 + z) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        return true;
+    }
+    /* the bulk stores have read their shared-memory source (called by every thread; only the issuing thread waits) */
+    __device__ __forceinline__ void store_wait()
+    {
+        if (store_pending && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        store_pending = false;
+    }
     /* one thread, once per kernel */
     __device__ __forceinline__ void mbar_init(uint64_t *bar)
     {
@@ -62,6 +97,7 @@ struct DevExec {
     }
     __device__ __forceinline__ void tile_wait(uint64_t *bar)
     {
+        store_wait();
         cp_async_wait_all();
         if (tma_pending) {
             const uint32_t b = smem_u32(bar);
@@ -155,14 +191,19 @@ struct DevExec {
 
 /* pass A, fast path: every tile.  C = the tile shape; the kernel stages it in the lean layout (LeanOf<C>) */
 template <class C>
-__global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap)
+__global__ void __launch_bounds__(RG_FAST_THREADS, RG_FAST_MINB) k_pass_a_fast(const Params P, const __grid_constant__ CUtensorMap tmap,
+                                                                               const __grid_constant__ CUtensorMap tmap_mask)
 {
     typedef typename LeanOf<C>::type L;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     FastSmem<L> &s = *reinterpret_cast<FastSmem<L> *>(smem_raw);
     DevExec<RG_FAST_THREADS> ex; ex.tmap = &tmap;
     ex.grid3d = gridDim.y * gridDim.z > 1 || (P.nty == 1 && P.ntz == 1);
-    if (P.use_tma) ex.mbar_init(&s.mbar);
+    ex.tmap_mask = &tmap_mask;
+    if (P.use_tma && threadIdx.x == 0) {                    /* the barrier that publishes this is the first one of the tile pass */
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32(&s.mbar)) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     const uint32_t tile = ex.grid3d ? (blockIdx.z * (uint32_t)P.nty + blockIdx.y) * (uint32_t)P.ntx + blockIdx.x : blockIdx.x;
     tile_pass_a_fast<L>(ex, P, tile, s);
 }
@@ -364,6 +405,7 @@ struct rg_ctx {
     dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     CUtensorMap last_tmap_fast;                /* the same image with the lean box of the fast labelling pass */
+    CUtensorMap last_tmap_mask;                /* the mask, box = one clearing store of the fast labelling pass */
     bool profile; cudaEvent_t ev[7]; bool ev_made;  /* optional per-kernel timing (rg_ctx_profile) */
     uint32_t last_full_tiles;                      /* tiles of the last call that overflowed the dense path (set by rg_ctx_status) */
 };
@@ -399,6 +441,24 @@ static bool make_tmap(CUtensorMap *tm, const uint8_t *base, int64_t nx, int64_t 
     if (strides[1] >= (1ull << 40)) return false;
     return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+/* uint8 mask [nz][ny][nx]; box = what one bulk store of the fast labelling pass clears (see DevExec::tma_clear_tile) */
+template <class C>
+static bool make_tmap_mask(CUtensorMap *tm, uint8_t *base, int64_t nx, int64_t ny, int64_t nz, int zero_bytes)
+{
+    tmap_encode_fn enc = get_tmap_encoder();
+    if (!enc) return false;
+    const int BR = C::TY < 32 ? C::TY : 32;
+    const int BZ = zero_bytes / (C::TX * BR) < C::TZ ? zero_bytes / (C::TX * BR) : C::TZ;
+    if (BZ < 1) return false;
+    cuuint64_t dims[3] = { (cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)nz };
+    cuuint64_t strides[2] = { (cuuint64_t)nx, (cuuint64_t)nx * (cuuint64_t)ny };
+    cuuint32_t box[3] = { (cuuint32_t)C::TX, (cuuint32_t)BR, (cuuint32_t)BZ };
+    cuuint32_t es[3] = { 1, 1, 1 };
+    if (strides[1] >= (1ull << 40)) return false;
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 struct Layout {
@@ -569,7 +629,8 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     const int64_t ey = ext_ylo<C>(P) + ext_yhi<C>(P), ez = ext_zlo<C>(P) + ext_zhi<C>(P);
     const uint8_t *map_base = d_image - (size_t)ext_zlo<C>(P) * nx * ny - (size_t)ext_ylo<C>(P) * nx;
     P.use_tma = (P.fast16 && make_tmap<C>(&c->last_tmap, map_base, nx, ny + ey, nz + ez)
-                 && make_tmap<typename LeanOf<C>::type>(&c->last_tmap_fast, map_base, nx, ny + ey, nz + ez)) ? 1 : 0;
+                 && make_tmap<typename LeanOf<C>::type>(&c->last_tmap_fast, map_base, nx, ny + ey, nz + ez)
+                 && make_tmap_mask<C>(&c->last_tmap_mask, d_mask, nx, ny, nz, (int)sizeof(((FastSmem<typename LeanOf<C>::type> *)0)->tab))) ? 1 : 0;
     P.rec = (TileRec *)(ws + L.off_rec); P.ent = (uint16_t *)(ws + L.off_ent);
     P.nparent = (uint32_t *)(ws + L.off_npar); P.nrep = (uint16_t *)(ws + L.off_nrep);
     P.counters = (uint32_t *)(ws + L.off_ctr); P.node_cap = L.node_cap;
@@ -598,7 +659,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
         static int pad = -1;                                        /* tuning: RG_FAST_PAD_SMEM=bytes lowers the CTAs per SM */
         if (pad < 0) { const char *e = getenv("RG_FAST_PAD_SMEM"); pad = e ? atoi(e) : 0;
                        if (pad) cudaFuncSetAttribute(k_pass_a_fast<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FastSmem<typename LeanOf<C>::type>) + pad); }
-        k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<typename LeanOf<C>::type>) + pad, st>>>(P, c->last_tmap_fast);
+        k_pass_a_fast<C><<<tile_grid, RG_FAST_THREADS, sizeof(FastSmem<typename LeanOf<C>::type>) + pad, st>>>(P, c->last_tmap_fast, c->last_tmap_mask);
     }
     if (c->profile) cudaEventRecord(c->ev[2], st);
     if (!P.debug_stop || P.debug_stop >= 10) k_pass_a_full<C><<<RG_PERSISTENT_CTAS, RG_THREADS, sizeof(TileSmem<C>), st>>>(P, c->last_tmap);

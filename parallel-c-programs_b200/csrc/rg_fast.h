@@ -42,6 +42,9 @@ struct alignas(128) FastSmem {
         uint8_t img[C::IMG_BYTES];                /* the staged tile */
         DenseSmem<C> d;                           /* ... and, once its link words are in registers, the state of the dense labelling path (rg_dense.h) */
     } u;
+    /* open addressing: representative + 1, 0 = empty (32-bit: shared-memory CAS is native).  All zeros until the walks start:
+       the source of the bulk stores that clear the tile's part of the mask (128-byte aligned for them). */
+    alignas(128) uint32_t tab[HASH_N];
     uint64_t mbar;
     /* Storage shared over time.  The cross-tile edge words and their prefix sums are dead once the edge list exists and the
        list of the longer walks takes their place; that list and the x = TX halo column (lean layout: one byte per (y, z),
@@ -57,7 +60,6 @@ struct alignas(128) FastSmem {
         uint16_t slotid[HASH_N];                  /* dense node id of each occupied slot (scan after the walks) */
     } v;
     uint16_t ent_root[FAST_ENT_MAX];              /* per edge: start voxel, later the hash slot of its component */
-    alignas(16) uint32_t tab[HASH_N];             /* open addressing: representative + 1, 0 = empty (32-bit: shared-memory CAS is native) */
     alignas(16) uint32_t seedtab[HASH_N / 32];    /* bit per slot: the component holds a seed */
     uint32_t scal[24];                            /* SC_* and, from SC_CNT0 on, the six face-list lengths */
     uint32_t scan_scratch[40];
@@ -227,10 +229,13 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     const int vy = (int)((P.ny - y0) < C::TY ? (P.ny - y0) : C::TY);
     const int vz = (int)((P.nz - z0) < C::TZ ? (P.nz - z0) : C::TZ);
 
-    if (!ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.img, x0, y0, z0, true);   /* copies are in flight from here */
-    if (P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0);          /* fire-and-forget stores: they fill the load's latency */
-    ex.pfor(C::FW_TOTAL, [&](int i) { s.v.e.u.f.fmask[i] = 0; });
     ex.pfor(HASH_N / 4, [&](int i) { st128(&s.tab[4 * i], u32x4{0, 0, 0, 0}); });
+    ex.sync_async_smem();                                           /* the zeros are visible to the copy engine; the load barrier is initialised */
+    if (!ex.template tma_tile<C>(P, s.u.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.img, x0, y0, z0, true);   /* copies are in flight from here */
+    /* the tile's part of the mask is cleared while the load is in flight: bulk stores of the (still empty) hash table,
+       one instruction each, or -- unaligned buffers, no TMA -- fire-and-forget vector stores */
+    if (P.mask_prezeroed && !ex.template tma_clear_tile<C>(P, s.tab, (int)sizeof(s.tab), x0, y0, z0)) zero_tile<C>(ex, P, x0, y0, z0);
+    ex.pfor(C::FW_TOTAL, [&](int i) { s.v.e.u.f.fmask[i] = 0; });
     auto load_xr = [&]() {
         if (C::XR) return;
         /* lean layout: the x = TX column is not in the staged box; one byte per (y, z) straight from the image (the

@@ -34,6 +34,8 @@ struct HostExec {
         }
     }
     void sync() {}
+    void sync_async_smem() {}
+    template <class C> bool tma_clear_tile(const Params &, const void *, int, int64_t, int64_t, int64_t) { return false; }
     bool sync_or(bool p) { return p; }
     template <class C> bool tma_tile(const Params &, uint8_t *, uint64_t *, int64_t, int64_t, int64_t) { return false; }
     void tile_wait(uint64_t *) {}
