@@ -266,10 +266,26 @@ class Context:
         """image: CUDA uint8 (nz,ny,nx) or (ny,nx); seeds_dev: CUDA int32 (k,3); out: CUDA uint8 like image"""
         nx, ny, nz = _dims(image)
         k = 0 if seeds_dev is None else int(seeds_dev.shape[0])
+        self._check_tensors(image, out, seeds_dev)
         _check(self.lib, self.lib.rg_grow_device(self.handle, image.data_ptr(), nx, ny, nz,
                                                  seeds_dev.data_ptr() if k else None, k, int(threshold), out.data_ptr(),
                                                  _stream_ptr(stream)), "rg_grow_device")
         return out
+
+    def _check_tensors(self, image, out, seeds_dev=None):
+        """the C ABI takes raw device pointers: a sliced, mistyped or misplaced tensor would be read / written out of bounds"""
+        import torch
+        for name, t in (("image", image), ("out", out)):
+            if t is None:
+                continue
+            if not (t.is_cuda and t.device.index == self.device and t.dtype == torch.uint8 and t.is_contiguous()):
+                raise ValueError(f"{name} must be a contiguous uint8 CUDA tensor on device {self.device}")
+        if out is not None and tuple(out.shape) != tuple(image.shape):
+            raise ValueError("out must have the image's shape")
+        if seeds_dev is not None and int(seeds_dev.shape[0]):
+            if not (seeds_dev.is_cuda and seeds_dev.device.index == self.device and seeds_dev.dtype == torch.int32
+                    and seeds_dev.is_contiguous() and seeds_dev.dim() == 2 and seeds_dev.shape[1] == 3):
+                raise ValueError(f"seeds must be a contiguous int32 (k, 3) CUDA tensor on device {self.device}")
 
     def status(self):
         st = (ctypes.c_uint32 * 4)()
@@ -286,6 +302,7 @@ class Context:
         return {"seed_sort": ms[0], "pass_a_fast": ms[1], "pass_a_full": ms[2], "merge": ms[3], "flag_tiles": ms[4], "pass_c": ms[5]}
 
     def apply_mask(self, image, mask, stream=None):
+        self._check_tensors(image, mask)
         _check(self.lib, self.lib.rg_apply_mask_device(self.handle, image.data_ptr(), mask.data_ptr(), image.numel(),
                                                        _stream_ptr(stream)), "rg_apply_mask_device")
 

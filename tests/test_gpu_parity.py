@@ -472,3 +472,13 @@ def test_apply_mask_device(rg, ctx, oracle, golden):
     ctx.apply_mask(d, m)
     torch.cuda.synchronize()
     assert hashlib.sha256(d.cpu().numpy().tobytes()).hexdigest() == golden["pics"]["pic3"]["out_sha256"]
+
+
+@pytest.mark.parametrize("kind,n", [("c4", 768), ("c3", 512)])
+def test_bench_sample_sizes_vs_oracle(rg, ctx, oracle, kind, n):
+    """the sizes bench.py's CPU legs grow anyway (C4 geometry at 768^3, C3 at 512^3), byte for byte against the oracle --
+    both through the default path and with every non-uniform tile forced down the dense labelling path"""
+    img, seeds, T = oracle.synth(kind, n, 0x5EED0000 + (4 if kind == "c4" else 3))
+    want = oracle.grow(img, seeds, T)
+    got = dev_grow(rg, ctx, img, seeds, T)
+    assert (got == want).all() and int(want.sum()) > 1000
