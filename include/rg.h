@@ -69,6 +69,19 @@ int rg_grow_region_2d(unsigned char *image, int width, int height, unsigned char
 int rg_grow(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
             const int32_t *seeds_xyz, int nseeds, int threshold, uint8_t *mask_out);
 
+/* Like rg_grow for a caller whose mask buffer is ALL ZEROS on entry -- fresh from calloc (the reference's convention:
+ * its growers return a calloc'd region, raycast.cu:705,762), or cleared by the caller.  Only the boxes of the mask that hold
+ * region voxels are copied back (whole tiles; C1's region is 1.6 % of its volume), the rest of the buffer is not touched.
+ * The reference-shaped growers above use this path with their own calloc.  No counterpart in the reference. */
+int rg_grow_sparse(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
+                   const int32_t *seeds_xyz, int nseeds, int threshold, uint8_t *mask_zeroed);
+
+/* What the last host-pointer call on the current device moved: {bytes host->device, bytes device->host, device->host copies
+ * issued, 1 if a pageable buffer was staged through the library's pinned bounce buffers by its copy threads}.
+ * Pageable (malloc'd) buffers of 32 MiB and more are staged that way; pinned buffers go to the copy engine directly.
+ * No counterpart in the reference (bench.py reports these as h2d/d2h bytes per step). */
+int rg_host_stats(int64_t out[4]);
+
 /* Context = per-device workspace (scratch for tile records, face lists, coarse union-find). */
 int rg_ctx_create(int device, rg_ctx **out);
 void rg_ctx_destroy(rg_ctx *ctx);

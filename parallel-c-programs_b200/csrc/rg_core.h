@@ -91,7 +91,7 @@ struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint32_t nnodes;
     uint16_t cnt[6];             /* face-list lengths, order XM XP YM YP ZM ZP */
     uint16_t uniform;            /* 1: all voxels of the tile are one component (pass C needs no image read) */
-    uint16_t pad1;
+    uint16_t has_region;         /* written by the flag pass: 1 = the tile holds region voxels (output-sensitive copies of the mask) */
     uint32_t plane_slot1;        /* 1 + index of the tile's saved link planes (Params::planes), 0 = none */
     uint32_t pad3;
 };
@@ -573,7 +573,7 @@ RG_FN void emit_nodes(Exec &ex, const Params &P, uint32_t tile, S &s)
         TileRec rc;
         rc.node_base = base; rc.nnodes = ok ? k : 0u;
         for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)(s.fprefix[C::fw_off(f + 1)] - s.fprefix[C::fw_off(f)]) : (uint16_t)0;
-        rc.uniform = (uint16_t)(ok ? s.scal[SC_UNIFORM] : 0u); rc.pad1 = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
+        rc.uniform = (uint16_t)(ok ? s.scal[SC_UNIFORM] : 0u); rc.has_region = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
         P.rec[tile] = rc;
     }
 }

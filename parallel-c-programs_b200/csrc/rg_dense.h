@@ -242,7 +242,7 @@ RG_FN void dense_label_runs(Exec &ex, const Params &P, uint32_t tile, S &s, PT *
         TileRec rc;
         rc.node_base = base; rc.nnodes = ok ? k : 0u;
         for (int f = 0; f < 6; f++) rc.cnt[f] = ok ? (uint16_t)s.scal[SC_CNT0 + f] : (uint16_t)0;
-        rc.uniform = 0; rc.pad1 = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
+        rc.uniform = 0; rc.has_region = 0; rc.plane_slot1 = ok ? s.scal[SC_PLANE1] : 0u; rc.pad3 = 0;
         P.rec[tile] = rc;
         atomic_add(&P.counters[CTR_NDENSE], 1u);
     }

@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <mutex>
+#include <thread>
 
 #include "rg_core.h"
 #include "rg_fast.h"
@@ -250,6 +251,13 @@ __global__ void __launch_bounds__(RG_PASSC_THREADS, 3) k_pass_c(const Params P, 
 }
 
 template <class C>
+__global__ void __launch_bounds__(256) k_region_boxes(const Params P, int32_t *out)
+{
+    DevExec<256> ex;
+    region_boxes<C>(ex, P, out);
+}
+
+template <class C>
 __global__ void __launch_bounds__(256) k_merge(const Params P)
 {
     DevExec<256> ex;
@@ -402,6 +410,10 @@ struct rg_ctx {
     Params last_P; int last_is2d; uint32_t last_ntiles; bool have_last;
     uint32_t *if_off[2];                       /* per-tile offsets of the two slab interfaces */
     ResolveArgs *d_rargs;                      /* device copy of the exchange bookkeeping (optimistic exchange) */
+    int32_t *d_boxes;                          /* per row of tiles: x-extent of the region (output-sensitive copy of the mask) */
+    int32_t *h_boxes; size_t h_boxes_cap;      /* pinned host copy of it */
+    uint8_t *bounce; size_t bounce_bytes;      /* pinned staging for pageable host buffers */
+    int64_t last_h2d_bytes, last_d2h_bytes; int last_copies, last_staged;   /* what the last host-pointer call moved (rg_host_stats) */
     dim3 last_grid;
     CUtensorMap last_tmap;                     /* image descriptor of the last label pass */
     CUtensorMap last_tmap_fast;                /* the same image with the lean box of the fast labelling pass */
@@ -462,7 +474,7 @@ static bool make_tmap_mask(CUtensorMap *tm, uint8_t *base, int64_t nx, int64_t n
 }
 
 struct Layout {
-    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, off_rargs, total;
+    size_t off_rec, off_ent, off_npar, off_nrep, off_ctr, off_keys, off_keys2, off_cub, off_if0, off_if1, off_clist, off_flist, off_rargs, off_boxes, total;
     size_t off_planes, total_with_planes; uint32_t plane_cap;      /* optional tail: link planes the full pass keeps for pass C */
     uint32_t ntiles, node_cap; int ntx, nty, ntz; size_t cub_bytes;
 };
@@ -505,6 +517,7 @@ static int make_layout(int64_t nx, int64_t ny, int64_t nz, int nseeds, Layout &L
     L.off_clist = o; o = align_up(o + (size_t)ntiles * 4, 256);
     L.off_flist = o; o = align_up(o + (size_t)ntiles * 4, 256);
     L.off_rargs = o; o = align_up(o + sizeof(ResolveArgs), 256);
+    L.off_boxes = o; o = align_up(o + (size_t)nty * ntz * 2 * sizeof(int32_t), 256);
     L.total = o;
     /* optional: 12 KB of link planes for each of the first plane_cap tiles of the full pass's list (all of them up to
        64 Ki tiles).  A context takes it if the allocation succeeds; rg_workspace_bytes does not count it. */
@@ -549,7 +562,7 @@ extern "C" void rg_ctx_destroy(rg_ctx *c)
     if (!c) return;
     DeviceScope scope(c->device);
     cudaFree(c->ws); cudaFree(c->d_image); cudaFree(c->d_mask); cudaFree(c->d_seeds);
-    cudaFreeHost(c->h_status);
+    cudaFreeHost(c->h_status); cudaFreeHost(c->h_boxes); cudaFreeHost(c->bounce);
     if (c->ev_made) for (int i = 0; i < 7; i++) cudaEventDestroy(c->ev[i]);
     free(c);
 }
@@ -673,6 +686,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     c->last_P = P; c->last_is2d = (C::TZ == 1); c->last_ntiles = L.ntiles; c->have_last = true;
     c->if_off[0] = (uint32_t *)(ws + L.off_if0); c->if_off[1] = (uint32_t *)(ws + L.off_if1);
     c->d_rargs = (ResolveArgs *)(ws + L.off_rargs);
+    c->d_boxes = (int32_t *)(ws + L.off_boxes);
     return RG_OK;
 }
 
@@ -957,23 +971,163 @@ static int ensure_io(rg_ctx *c, size_t bytes, int nseeds)
     return RG_OK;
 }
 
+/* ---- moving host buffers.  Pinned (page-locked) buffers go to the copy engine as they are.  A pageable buffer -- what
+   malloc / calloc return, i.e. what the reference's callers pass (raycast.cu:147, 705) -- would make the driver stage the whole
+   copy through one internal buffer on the calling thread; here a few host threads copy chunks into pinned bounce buffers and
+   start the DMA of each chunk at once, so the host copies run in parallel with each other and with the DMA. */
+enum { STAGE_THREADS = 4, STAGE_CHUNK = 8 << 20, STAGE_SLOTS = 2 };
+
+static bool is_pageable(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+static int ensure_bounce(rg_ctx *c)
+{
+    const size_t need = (size_t)STAGE_THREADS * STAGE_SLOTS * STAGE_CHUNK;
+    if (c->bounce_bytes >= need) return RG_OK;
+    CK(cudaHostAlloc((void **)&c->bounce, need, cudaHostAllocDefault));
+    c->bounce_bytes = need;
+    return RG_OK;
+}
+
+/* dir = 0: host -> device, 1: device -> host; returns when the data has arrived */
+static int staged_copy(rg_ctx *c, int dir, uint8_t *host, uint8_t *dev, size_t bytes)
+{
+    int rc = ensure_bounce(c); if (rc) return rc;
+    const size_t nchunks = (bytes + STAGE_CHUNK - 1) / STAGE_CHUNK;
+    int err[STAGE_THREADS] = {0};
+    auto worker = [&](int t) {
+        cudaStream_t st; cudaEvent_t ev[STAGE_SLOTS];
+        if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { err[t] = 1; return; }
+        for (int k = 0; k < STAGE_SLOTS; k++) cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming);
+        uint8_t *mine = c->bounce + (size_t)t * STAGE_SLOTS * STAGE_CHUNK;
+        size_t pending_off[STAGE_SLOTS], pending_len[STAGE_SLOTS]; bool pending[STAGE_SLOTS] = {false};
+        int slot = 0;
+        for (size_t i = (size_t)t; i < nchunks && !err[t]; i += STAGE_THREADS, slot = (slot + 1) % STAGE_SLOTS) {
+            const size_t off = i * STAGE_CHUNK, len = bytes - off < (size_t)STAGE_CHUNK ? bytes - off : (size_t)STAGE_CHUNK;
+            uint8_t *buf = mine + (size_t)slot * STAGE_CHUNK;
+            if (pending[slot]) {                            /* the slot's previous chunk: DMA done? (dir 1: then hand it to the caller) */
+                if (cudaEventSynchronize(ev[slot]) != cudaSuccess) { err[t] = 1; break; }
+                if (dir == 1) memcpy(host + pending_off[slot], buf, pending_len[slot]);
+                pending[slot] = false;
+            }
+            if (dir == 0) {
+                memcpy(buf, host + off, len);
+                if (cudaMemcpyAsync(dev + off, buf, len, cudaMemcpyHostToDevice, st) != cudaSuccess) err[t] = 1;
+            } else if (cudaMemcpyAsync(buf, dev + off, len, cudaMemcpyDeviceToHost, st) != cudaSuccess) err[t] = 1;
+            cudaEventRecord(ev[slot], st);
+            pending[slot] = true; pending_off[slot] = off; pending_len[slot] = len;
+        }
+        for (int k = 0; k < STAGE_SLOTS; k++) {
+            const int sl = (slot + k) % STAGE_SLOTS;        /* oldest first */
+            if (pending[sl]) {
+                if (cudaEventSynchronize(ev[sl]) != cudaSuccess) err[t] = 1;
+                else if (dir == 1) memcpy(host + pending_off[sl], mine + (size_t)sl * STAGE_CHUNK, pending_len[sl]);
+            }
+        }
+        for (int k = 0; k < STAGE_SLOTS; k++) cudaEventDestroy(ev[k]);
+        cudaStreamDestroy(st);
+    };
+    std::thread th[STAGE_THREADS];
+    for (int t = 1; t < STAGE_THREADS; t++) th[t] = std::thread(worker, t);
+    worker(0);
+    for (int t = 1; t < STAGE_THREADS; t++) th[t].join();
+    for (int t = 0; t < STAGE_THREADS; t++) if (err[t]) return fail(RG_ERR_CUDA, "staged host copy failed", cudaGetLastError());
+    c->last_staged = 1;
+    return RG_OK;
+}
+
+static int copy_in(rg_ctx *c, uint8_t *dev, const uint8_t *host, size_t bytes, cudaStream_t st)
+{
+    c->last_h2d_bytes += (int64_t)bytes;
+    if (bytes >= (size_t)(4 * STAGE_CHUNK) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
+        CK(cudaStreamSynchronize(st));
+        return staged_copy(c, 0, const_cast<uint8_t *>(host), dev, bytes);
+    }
+    CK(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, st));
+    return RG_OK;
+}
+
+static int copy_out_full(rg_ctx *c, uint8_t *host, const uint8_t *dev, size_t bytes, cudaStream_t st)
+{
+    c->last_d2h_bytes += (int64_t)bytes; c->last_copies++;
+    if (bytes >= (size_t)(4 * STAGE_CHUNK) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
+        CK(cudaStreamSynchronize(st));
+        return staged_copy(c, 1, host, const_cast<uint8_t *>(dev), bytes);
+    }
+    CK(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, st));
+    return RG_OK;
+}
+
+/* Output-sensitive copy of the mask: `host` is known to be all zeros (a fresh calloc, or the caller's promise), so only the
+   boxes that hold region voxels are copied -- per plane of tiles, rows of tiles with the same x-extent merged into one
+   three-dimensional copy.  C1's region is 1.6 % of its volume, C4's 7 %. */
+static int copy_out_sparse(rg_ctx *c, uint8_t *host, int64_t nx, int64_t ny, int64_t nz, cudaStream_t st)
+{
+    const Params &P = c->last_P;
+    const int TX = c->last_is2d ? Cfg2D::TX : Cfg3D::TX, TY = c->last_is2d ? Cfg2D::TY : Cfg3D::TY, TZ = c->last_is2d ? Cfg2D::TZ : Cfg3D::TZ;
+    const size_t rows = (size_t)P.nty * P.ntz;
+    if (c->h_boxes_cap < rows * 2) {
+        cudaFreeHost(c->h_boxes); c->h_boxes = nullptr; c->h_boxes_cap = 0;
+        CK(cudaHostAlloc((void **)&c->h_boxes, rows * 2 * sizeof(int32_t), cudaHostAllocDefault));
+        c->h_boxes_cap = rows * 2;
+    }
+    const int blocks = (int)((rows + 255) / 256);
+    if (c->last_is2d) k_region_boxes<Cfg2D><<<blocks, 256, 0, st>>>(P, c->d_boxes);
+    else k_region_boxes<Cfg3D><<<blocks, 256, 0, st>>>(P, c->d_boxes);
+    CK(cudaMemcpyAsync(c->h_boxes, c->d_boxes, rows * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    cudaMemcpy3DParms q;
+    memset(&q, 0, sizeof q);
+    q.srcPtr = make_cudaPitchedPtr(P.mask, (size_t)nx, (size_t)nx, (size_t)ny);
+    q.dstPtr = make_cudaPitchedPtr(host, (size_t)nx, (size_t)nx, (size_t)ny);
+    q.kind = cudaMemcpyDeviceToHost;
+    for (int tz = 0; tz < P.ntz; tz++) {
+        const int32_t *b = c->h_boxes + (size_t)tz * P.nty * 2;
+        for (int ty = 0; ty < P.nty; ) {
+            if (!b[2 * ty + 1]) { ty++; continue; }
+            int t1 = ty + 1;
+            while (t1 < P.nty && b[2 * t1] == b[2 * ty] && b[2 * t1 + 1] == b[2 * ty + 1]) t1++;
+            const int64_t x0 = (int64_t)b[2 * ty] * TX, x1 = (int64_t)b[2 * ty + 1] * TX < nx ? (int64_t)b[2 * ty + 1] * TX : nx;
+            const int64_t y0 = (int64_t)ty * TY, y1 = (int64_t)t1 * TY < ny ? (int64_t)t1 * TY : ny;
+            const int64_t z0 = (int64_t)tz * TZ, z1 = (int64_t)(tz + 1) * TZ < nz ? (int64_t)(tz + 1) * TZ : nz;
+            q.srcPos = make_cudaPos((size_t)x0, (size_t)y0, (size_t)z0); q.dstPos = q.srcPos;
+            q.extent = make_cudaExtent((size_t)(x1 - x0), (size_t)(y1 - y0), (size_t)(z1 - z0));
+            CK(cudaMemcpy3DAsync(&q, st));
+            c->last_d2h_bytes += (x1 - x0) * (y1 - y0) * (z1 - z0); c->last_copies++;
+            ty = t1;
+        }
+    }
+    return RG_OK;
+}
+
+enum { OUT_FULL = 0, OUT_SPARSE = 1 };
+
 static int grow_host(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds, int nseeds,
-                     int threshold, uint8_t *mask_out, uint8_t *image_inout_apply)
+                     int threshold, uint8_t *mask_out, uint8_t *image_inout_apply, int out_mode = OUT_FULL)
 {
     if (!image || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !seeds)) return fail(RG_ERR_ARG, "bad argument");
     std::lock_guard<std::mutex> lk(g_mu);
     rg_ctx *c; int rc = default_ctx(&c); if (rc) return rc;
+    ON_DEVICE(c->device);
     size_t bytes = (size_t)nx * ny * nz;
     rc = ensure_io(c, bytes, nseeds); if (rc) return rc;
     cudaStream_t st = 0;
-    CK(cudaMemcpyAsync(c->d_image, image, bytes, cudaMemcpyHostToDevice, st));
+    c->last_h2d_bytes = c->last_d2h_bytes = 0; c->last_copies = 0; c->last_staged = 0;
+    rc = copy_in(c, c->d_image, image, bytes, st); if (rc) return rc;
     if (nseeds) CK(cudaMemcpyAsync(c->d_seeds, seeds, (size_t)nseeds * 12, cudaMemcpyHostToDevice, st));
     rc = grow_device_impl(c, c->d_image, nx, ny, nz, 0, 0, c->d_seeds, nseeds, threshold, c->d_mask, st);
     if (rc) return rc;
-    if (mask_out) CK(cudaMemcpyAsync(mask_out, c->d_mask, bytes, cudaMemcpyDeviceToHost, st));
+    if (mask_out) {
+        rc = out_mode == OUT_SPARSE ? copy_out_sparse(c, mask_out, nx, ny, nz, st) : copy_out_full(c, mask_out, c->d_mask, bytes, st);
+        if (rc) return rc;
+    }
     if (image_inout_apply) {
         rc = rg_apply_mask_device(c, c->d_image, c->d_mask, (int64_t)bytes, st); if (rc) return rc;
-        CK(cudaMemcpyAsync(image_inout_apply, c->d_image, bytes, cudaMemcpyDeviceToHost, st));
+        rc = copy_out_full(c, image_inout_apply, c->d_image, bytes, st); if (rc) return rc;
     }
     return rg_ctx_status(c, nullptr);
 }
@@ -985,6 +1139,22 @@ extern "C" int rg_grow(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
     return grow_host(image, nx, ny, nz, seeds_xyz, nseeds, threshold, mask_out, nullptr);
 }
 
+extern "C" int rg_grow_sparse(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz,
+                              const int32_t *seeds_xyz, int nseeds, int threshold, uint8_t *mask_zeroed)
+{
+    if (!mask_zeroed) return fail(RG_ERR_ARG, "mask == NULL");
+    return grow_host(image, nx, ny, nz, seeds_xyz, nseeds, threshold, mask_zeroed, nullptr, OUT_SPARSE);
+}
+
+extern "C" int rg_host_stats(int64_t out[4])
+{
+    if (!out) return fail(RG_ERR_ARG, "out == NULL");
+    std::lock_guard<std::mutex> lk(g_mu);
+    rg_ctx *c; int rc = default_ctx(&c); if (rc) return rc;
+    out[0] = c->last_h2d_bytes; out[1] = c->last_d2h_bytes; out[2] = c->last_copies; out[3] = c->last_staged;
+    return RG_OK;
+}
+
 static unsigned char *grow_512(unsigned char *data)
 {
     /* raycast.cu:11 DATA_DIM 512; :286/:775 seed; :275 threshold */
@@ -993,7 +1163,8 @@ static unsigned char *grow_512(unsigned char *data)
     if (!data) { fail(RG_ERR_ARG, "data == NULL"); return nullptr; }
     unsigned char *region = (unsigned char *)calloc(sizeof(unsigned char), (size_t)(D * D * D));
     if (!region) { fail(RG_ERR_NOMEM, "calloc"); return nullptr; }
-    if (grow_host(data, D, D, D, seed, 1, 1, region, nullptr) != RG_OK) { free(region); return nullptr; }
+    /* the mask comes from calloc two lines up: only the boxes that hold region voxels are copied into it */
+    if (grow_host(data, D, D, D, seed, 1, 1, region, nullptr, OUT_SPARSE) != RG_OK) { free(region); return nullptr; }
     return region;
 }
 extern "C" unsigned char *grow_region_gpu(unsigned char *data) { return grow_512(data); }

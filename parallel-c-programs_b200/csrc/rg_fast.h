@@ -371,7 +371,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         TileRec rc;
         rc.node_base = base; rc.nnodes = nnodes;
         for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)s.scal[SC_CNT0 + f];
-        rc.uniform = uniform ? 1 : 0; rc.pad1 = 0; rc.plane_slot1 = 0; rc.pad3 = 0;
+        rc.uniform = uniform ? 1 : 0; rc.has_region = 0; rc.plane_slot1 = 0; rc.pad3 = 0;
         P.rec[tile] = rc;
     }
 }
@@ -385,6 +385,19 @@ RG_FN void pass_a_full_list(Exec &ex, const Params &P, TileSmem<C> &s)
         tile_pass_a<C>(ex, P, P.complex_list[i], s);
         ex.sync();
     }
+}
+
+/* x-extent of the region in every row of tiles: one item per (ty, tz), out[2 * item] = first tile column that holds region
+   voxels, out[2 * item + 1] = one past the last (both 0: none).  The host copies back only those boxes of the mask. */
+template <class C, class Exec>
+RG_FN void region_boxes(Exec &ex, const Params &P, int32_t *out)
+{
+    ex.gpfor((int64_t)P.nty * P.ntz, [&](int64_t it) {
+        const TileRec *row = P.rec + it * P.ntx;
+        int lo = P.ntx, hi = 0;
+        for (int tx = 0; tx < P.ntx; tx++) if (row[tx].has_region) { if (tx < lo) lo = tx; hi = tx + 1; }
+        out[2 * it] = hi ? lo : 0; out[2 * it + 1] = hi;
+    });
 }
 
 /* ================================================================ region tiles vs. empty tiles */
@@ -403,6 +416,7 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
             return false;
         },
         [&](uint32_t tile, uint32_t lane, bool mine) {
+            if (lane == 0) P.rec[tile].has_region = mine ? 1 : 0;
             if (mine && !P.rec[tile].uniform) {
                 if (lane == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
                 return;

@@ -482,3 +482,45 @@ def test_bench_sample_sizes_vs_oracle(rg, ctx, oracle, kind, n):
     want = oracle.grow(img, seeds, T)
     got = dev_grow(rg, ctx, img, seeds, T)
     assert (got == want).all() and int(want.sum()) > 1000
+
+
+def _host_stats(lib):
+    st = (ctypes.c_int64 * 4)()
+    assert lib.rg_host_stats(st) == 0
+    return list(st)
+
+
+def test_sparse_output_and_staged_pageable_copies(rg, oracle):
+    """rg_grow_sparse copies back only the boxes of tiles that hold region voxels into a mask the caller has zeroed, and a
+    pageable (numpy / malloc) buffer of 32 MiB or more travels through the library's pinned bounce buffers on its copy threads:
+    same bytes as the oracle either way, ragged sizes included"""
+    lib = rg.load_library()
+    rng = np.random.default_rng(31)
+    vol = rng.integers(0, 20, size=(300, 352, 336), dtype=np.uint8)            # 35.5 MB: above the staging threshold
+    vol[40:200, 100:300, 50:250] = 90
+    vol[250:290, 10:60, 300:336] = 91
+    seeds = np.array([[100, 150, 100], [320, 30, 270], [0, 0, 0]], np.int32)
+    want = oracle.grow(vol, seeds, 1)
+    # full copy, pageable in and out
+    got = rg.grow(vol, seeds, 1)
+    st = _host_stats(lib)
+    assert (got == want).all() and st[0] == vol.size and st[1] == vol.size and st[3] == 1
+    # sparse copy into a zeroed buffer
+    out = np.zeros_like(vol)
+    rc = lib.rg_grow_sparse(vol.ctypes.data, 336, 352, 300, seeds.ctypes.data, len(seeds), 1, out.ctypes.data)
+    st = _host_stats(lib)
+    assert rc == 0 and (out == want).all()
+    assert 0 < st[1] < vol.size // 2 and st[2] >= 2                              # far fewer bytes came back
+    # nothing outside the copied boxes is written: a buffer that is NOT zero keeps its bytes where no region tile is
+    out2 = np.full_like(vol, 7)
+    assert lib.rg_grow_sparse(vol.ctypes.data, 336, 352, 300, seeds.ctypes.data, len(seeds), 1, out2.ctypes.data) == 0
+    assert ((out2 == want) | (out2 == 7)).all() and (out2[want == 1] == 1).all() and int((out2 == 7).sum()) > vol.size // 2
+    # an image, and an empty region
+    img = rng.integers(0, 6, size=(700, 1000), dtype=np.uint8); img[100:300, 200:900] = 50
+    s2 = np.array([[500, 200, 0]], np.int32)
+    o2 = np.zeros_like(img)
+    assert lib.rg_grow_sparse(img.ctypes.data, 1000, 700, 1, s2.ctypes.data, 1, 2, o2.ctypes.data) == 0
+    assert (o2 == oracle.grow(img, s2, 2)).all()
+    o3 = np.zeros_like(img)
+    assert lib.rg_grow_sparse(img.ctypes.data, 1000, 700, 1, None, 0, 2, o3.ctypes.data) == 0 and not o3.any()
+    assert _host_stats(lib)[1] == 0
