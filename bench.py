@@ -605,19 +605,59 @@ def run_e2e(torch, rgb200, lib, ctx, dist, dev, rank, world, wl, n, barrier, max
         torch.cuda.synchronize(); torch.cuda.empty_cache()
         nx, ny, nz = (n_e2e, n_e2e, 1) if dims == 2 else (n_e2e,) * 3
 
-        def call():
-            rc = lib.rg_grow(h_img.data_ptr(), nx, ny, nz, seeds_np.ctypes.data, len(seeds_np), T, h_out.data_ptr())
-            if rc != 0:
-                raise RuntimeError(lib.rg_last_error().decode())
-        call()                                                # warm-up: allocates the library's staging buffers
-        t0 = time.perf_counter()
-        for _ in range(steps):
-            call()
-        sec = (time.perf_counter() - t0) / steps
+        def stats():
+            st = (ctypes.c_int64 * 4)()
+            lib.rg_host_stats(st)
+            return list(st)
+
+        def timed(fn, img_ptr, out_ptr, reps=steps):
+            def call():
+                rc = fn(img_ptr, nx, ny, nz, seeds_np.ctypes.data, len(seeds_np), T, out_ptr)
+                if rc != 0:
+                    raise RuntimeError(lib.rg_last_error().decode())
+            call()                                            # warm-up: allocates the library's staging buffers
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                call()
+            sec = (time.perf_counter() - t0) / reps
+            h2d, d2h, ncopies, staged = stats()
+            return {"value": nvox / sec / 1e9, "ms_per_step": sec * 1e3, "h2d_bytes_per_step": int(h2d + 12 * len(seeds_np)),
+                    "d2h_bytes_per_step": int(d2h), "d2h_copies": int(ncopies), "staged_through_bounce_buffers": bool(staged)}
+
+        # (1) nothing assumed about the caller's mask buffer: every byte of it is written (rg_grow)
+        full = timed(lib.rg_grow, h_img.data_ptr(), h_out.data_ptr())
+        cnt_full = int(h_out.sum(dtype=torch.int64))
+        # (2) the reference's convention: the mask buffer is zero when the grower gets it (its growers calloc it, raycast.cu:705,762);
+        #     only the boxes of tiles that hold region voxels come back.  Cleared once here, before the loop: every step grows the
+        #     same volume, so every step rewrites the same boxes.
+        h_out.zero_()
+        sparse = timed(lib.rg_grow_sparse, h_img.data_ptr(), h_out.data_ptr())
         cnt = int(h_out.sum(dtype=torch.int64))
-        return {"value": nvox / sec / 1e9, "unit": "Gvoxels/s", "h2d_bytes_per_step": int(nvox + 12 * len(seeds_np)),
-                "d2h_bytes_per_step": int(nvox), "ms_per_step": sec * 1e3, "n": n_e2e, "region_voxels": cnt,
-                "api": "rg_grow (C ABI, pinned host image in, pinned host mask out)", "timer": "host wall clock around the synchronous call"}
+        res = {"value": sparse["value"], "unit": "Gvoxels/s", "h2d_bytes_per_step": sparse["h2d_bytes_per_step"],
+               "d2h_bytes_per_step": sparse["d2h_bytes_per_step"], "ms_per_step": sparse["ms_per_step"], "n": n_e2e, "region_voxels": cnt,
+               "api": "rg_grow_sparse (C ABI): pinned host image in, pinned host mask out; the mask buffer was zeroed once before the loop "
+                      "(the reference's growers hand out calloc'd masks) and only the boxes that hold region voxels are copied back",
+               "timer": "host wall clock around the synchronous call",
+               "variants": {"pinned_sparse_out": sparse,
+                            "pinned_full_copy": dict(full, api="rg_grow: every byte of the caller's mask is written", region_voxels=cnt_full)}}
+        # (3) pageable buffers (plain malloc / numpy), as the reference's callers have them
+        if 7 * need_gb < avail_gb:
+            try:
+                p_img = np.empty(shape, np.uint8); p_img[...] = h_img.numpy()
+                p_out = np.zeros(shape, np.uint8)
+                res["variants"]["pageable_sparse_out"] = dict(timed(lib.rg_grow_sparse, p_img.ctypes.data, p_out.ctypes.data),
+                                                              api="rg_grow_sparse, numpy (pageable) image in, zero-initialised pageable mask out")
+                ok1 = int(p_out.sum(dtype=np.int64)) == cnt
+                res["variants"]["pageable_full_copy"] = dict(timed(lib.rg_grow, p_img.ctypes.data, p_out.ctypes.data, 1),
+                                                             api="rg_grow, numpy (pageable) image in and mask out")
+                res["variants"]["pageable_results_match"] = bool(ok1 and int(p_out.sum(dtype=np.int64)) == cnt)
+                del p_img, p_out
+            except Exception as e:
+                res["variants"]["pageable_error"] = repr(e)
+        else:
+            res["variants"]["pageable"] = f"skipped: {avail_gb:.0f} GB of host memory available, 4 buffers of {need_gb / 2:.1f} GB wanted"
+        res["results_match"] = bool(cnt == cnt_full)
+        return res
     # N > 1: every rank moves its slab (+ halo planes) host->device, grows, and reads its mask slab back
     g = rgb200.SlabGrower(lib, ctx.handle, n, n, 1 if dims == 2 else n, rank, world, dev)
     plane = g.plane
