@@ -975,7 +975,16 @@ static int ensure_io(rg_ctx *c, size_t bytes, int nseeds)
    malloc / calloc return, i.e. what the reference's callers pass (raycast.cu:147, 705) -- would make the driver stage the whole
    copy through one internal buffer on the calling thread; here a few host threads copy chunks into pinned bounce buffers and
    start the DMA of each chunk at once, so the host copies run in parallel with each other and with the DMA. */
-enum { STAGE_THREADS = 4, STAGE_CHUNK = 8 << 20, STAGE_SLOTS = 2 };
+enum { STAGE_THREADS_MAX = 16, STAGE_CHUNK = 4 << 20, STAGE_SLOTS = 2 };
+static int stage_threads()
+{
+    static const int n = [] {
+        const char *e = getenv("RG_STAGE_THREADS");             /* tuning aid */
+        int v = e ? atoi(e) : (int)(std::thread::hardware_concurrency() / 2);
+        return v < 1 ? 1 : v > STAGE_THREADS_MAX ? STAGE_THREADS_MAX : v;
+    }();
+    return n;
+}
 
 static bool is_pageable(const void *p)
 {
@@ -986,7 +995,7 @@ static bool is_pageable(const void *p)
 
 static int ensure_bounce(rg_ctx *c)
 {
-    const size_t need = (size_t)STAGE_THREADS * STAGE_SLOTS * STAGE_CHUNK;
+    const size_t need = (size_t)STAGE_THREADS_MAX * STAGE_SLOTS * STAGE_CHUNK;
     if (c->bounce_bytes >= need) return RG_OK;
     CK(cudaHostAlloc((void **)&c->bounce, need, cudaHostAllocDefault));
     c->bounce_bytes = need;
@@ -998,7 +1007,8 @@ static int staged_copy(rg_ctx *c, int dir, uint8_t *host, uint8_t *dev, size_t b
 {
     int rc = ensure_bounce(c); if (rc) return rc;
     const size_t nchunks = (bytes + STAGE_CHUNK - 1) / STAGE_CHUNK;
-    int err[STAGE_THREADS] = {0};
+    const int nthreads = stage_threads();
+    int err[STAGE_THREADS_MAX] = {0};
     auto worker = [&](int t) {
         cudaStream_t st; cudaEvent_t ev[STAGE_SLOTS];
         if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { err[t] = 1; return; }
@@ -1006,7 +1016,7 @@ static int staged_copy(rg_ctx *c, int dir, uint8_t *host, uint8_t *dev, size_t b
         uint8_t *mine = c->bounce + (size_t)t * STAGE_SLOTS * STAGE_CHUNK;
         size_t pending_off[STAGE_SLOTS], pending_len[STAGE_SLOTS]; bool pending[STAGE_SLOTS] = {false};
         int slot = 0;
-        for (size_t i = (size_t)t; i < nchunks && !err[t]; i += STAGE_THREADS, slot = (slot + 1) % STAGE_SLOTS) {
+        for (size_t i = (size_t)t; i < nchunks && !err[t]; i += (size_t)nthreads, slot = (slot + 1) % STAGE_SLOTS) {
             const size_t off = i * STAGE_CHUNK, len = bytes - off < (size_t)STAGE_CHUNK ? bytes - off : (size_t)STAGE_CHUNK;
             uint8_t *buf = mine + (size_t)slot * STAGE_CHUNK;
             if (pending[slot]) {                            /* the slot's previous chunk: DMA done? (dir 1: then hand it to the caller) */
@@ -1031,11 +1041,11 @@ static int staged_copy(rg_ctx *c, int dir, uint8_t *host, uint8_t *dev, size_t b
         for (int k = 0; k < STAGE_SLOTS; k++) cudaEventDestroy(ev[k]);
         cudaStreamDestroy(st);
     };
-    std::thread th[STAGE_THREADS];
-    for (int t = 1; t < STAGE_THREADS; t++) th[t] = std::thread(worker, t);
+    std::thread th[STAGE_THREADS_MAX];
+    for (int t = 1; t < nthreads; t++) th[t] = std::thread(worker, t);
     worker(0);
-    for (int t = 1; t < STAGE_THREADS; t++) th[t].join();
-    for (int t = 0; t < STAGE_THREADS; t++) if (err[t]) return fail(RG_ERR_CUDA, "staged host copy failed", cudaGetLastError());
+    for (int t = 1; t < nthreads; t++) th[t].join();
+    for (int t = 0; t < nthreads; t++) if (err[t]) return fail(RG_ERR_CUDA, "staged host copy failed", cudaGetLastError());
     c->last_staged = 1;
     return RG_OK;
 }
@@ -1043,7 +1053,7 @@ static int staged_copy(rg_ctx *c, int dir, uint8_t *host, uint8_t *dev, size_t b
 static int copy_in(rg_ctx *c, uint8_t *dev, const uint8_t *host, size_t bytes, cudaStream_t st)
 {
     c->last_h2d_bytes += (int64_t)bytes;
-    if (bytes >= (size_t)(4 * STAGE_CHUNK) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
+    if (bytes >= (size_t)(32 << 20) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
         CK(cudaStreamSynchronize(st));
         return staged_copy(c, 0, const_cast<uint8_t *>(host), dev, bytes);
     }
@@ -1054,7 +1064,7 @@ static int copy_in(rg_ctx *c, uint8_t *dev, const uint8_t *host, size_t bytes, c
 static int copy_out_full(rg_ctx *c, uint8_t *host, const uint8_t *dev, size_t bytes, cudaStream_t st)
 {
     c->last_d2h_bytes += (int64_t)bytes; c->last_copies++;
-    if (bytes >= (size_t)(4 * STAGE_CHUNK) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
+    if (bytes >= (size_t)(32 << 20) && !getenv("RG_NO_STAGING") && is_pageable(host)) {
         CK(cudaStreamSynchronize(st));
         return staged_copy(c, 1, host, const_cast<uint8_t *>(dev), bytes);
     }
