@@ -150,6 +150,21 @@ int rg_raycast_device(const uint8_t *d_data, const uint8_t *d_region, int data_d
 
 const char *rg_last_error(void);
 
+/* ---- one host image over several GPUs, one process -------------------------------------------- */
+/* Replaces the whole of region.c's main() sequence distribute_image -> distribute_image_halo -> grow_region (with its
+ * exchange()/finished() rounds) -> gather_region (region.c:106-246, 250-353, 391-440, 591-597) for a C host that owns
+ * several GPUs: the volume is cut into one z-slab per entry of `devices` (an image, nz == 1, into row slabs), every slab
+ * and its neighbours' boundary planes are copied from `image`, each device labels its slab, the interface lists are moved
+ * between the devices with peer copies and resolved in ONE exchange, and every slab's mask lands in `mask_out`.
+ * Same result as rg_grow, whatever the number of devices.  devices[] may name a GPU more than once (several slabs on one
+ * GPU).  flags: RG_MULTI_MASK_ZEROED = mask_out is all zeros on entry (calloc), copy back only the boxes that hold region
+ * voxels.  phase_ms (may be NULL) receives {whole call, scatter + label + export, exchange + output + gather, slabs used}
+ * in host milliseconds.  The first call allocates per-device buffers and contexts (kept for later calls of the same or a
+ * smaller size): that cold call is what a one-shot program pays. */
+#define RG_MULTI_MASK_ZEROED 1
+int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds_xyz, int nseeds,
+                  int threshold, uint8_t *mask_out, const int *devices, int ndev, int flags, float *phase_ms);
+
 /* ---- z-slab (multi-GPU) phases ------------------------------------------------------------- */
 /* Together these replace the distributed half of 2-mpi-region-growing/region.c -- exchange()
  * (:250-353), add_halo_to_stack() (:355-387), finished() (:435-440) and the static image-halo

@@ -13,6 +13,9 @@
 #include <string.h>
 #include <mutex>
 #include <thread>
+#include <vector>
+#include <functional>
+#include <chrono>
 
 #include "rg_core.h"
 #include "rg_fast.h"
@@ -1280,4 +1283,162 @@ extern "C" int rg_noalloc_status(uint32_t stats[4], void *stream)
         return RG_ERR_INTERNAL;
     }
     return RG_OK;
+}
+
+/* ------------------------------------------------------------------ one host image over several GPUs, from C
+ *
+ * rg_grow_multi is the whole of region.c's main() (region.c:582-604) for a C host with several GPUs in ONE process:
+ * distribute_image + distribute_image_halo (region.c:106-246: every slab and its two boundary planes come straight from the
+ * host image), grow per slab, one interface exchange in place of the exchange()/finished() rounds (region.c:250-353,
+ * 435-440; lists move between the devices with cudaMemcpyPeerAsync), gather_region (region.c:391-432: every slab's mask
+ * goes back into the caller's mask).  Volumes are cut along z, images (nz == 1) along y.  One host thread per slab drives
+ * its device; the only host-side meeting point is the one where the interface list lengths become known.
+ * A device may be named more than once (several slabs on one GPU) -- that is how the single-GPU tests exercise the exchange.
+ */
+struct MultiSlab {
+    int device; rg_ctx *ctx; cudaStream_t st;
+    uint8_t *buf; size_t buf_bytes; uint8_t *mask; size_t mask_bytes;
+    int32_t *seeds; size_t seeds_cap;
+    uint32_t *lists; size_t cap;                /* [2][cap] own interface lists */
+    uint32_t *counts_d; uint32_t *counts_h;     /* {lower entries, upper entries, node id space, -} */
+    uint32_t *gathered; size_t gathered_words; uint32_t *xpar; size_t xpar_words;
+    int rc; char err[256];
+};
+static MultiSlab g_multi[RESOLVE_MAX_RANKS];
+static std::mutex g_multi_mu;
+
+static int multi_fail(MultiSlab &m, int code) { m.rc = code; snprintf(m.err, sizeof m.err, "%s", g_err); return code; }
+#define MCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(RG_ERR_CUDA, #call, e_); return multi_fail(m, RG_ERR_CUDA); } } while (0)
+
+template <class T> static int multi_room(MultiSlab &m, T *&p, size_t &have, size_t want)
+{
+    if (have >= want) return RG_OK;
+    if (p) { cudaStreamSynchronize(m.st); cudaFree(p); p = nullptr; have = 0; }
+    MCK(cudaMalloc((void **)&p, want * sizeof(T)));
+    have = want;
+    return RG_OK;
+}
+
+extern "C" int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds_xyz, int nseeds,
+                             int threshold, uint8_t *mask_out, const int *devices, int ndev, int flags, float *phase_ms)
+{
+    if (!image || !mask_out || nx <= 0 || ny <= 0 || nz <= 0 || nseeds < 0 || (nseeds > 0 && !seeds_xyz) || !devices || ndev < 1)
+        return fail(RG_ERR_ARG, "bad argument");
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess || have == 0) return fail(RG_ERR_CUDA, "no CUDA device (this library has no CPU path)");
+    for (int g = 0; g < ndev; g++) if (devices[g] < 0 || devices[g] >= have) return fail(RG_ERR_ARG, "bad device index");
+    const bool rows = nz == 1;
+    const int64_t na = rows ? ny : nz, plane = rows ? nx : nx * ny;
+    int G = ndev > RESOLVE_MAX_RANKS ? RESOLVE_MAX_RANKS : ndev;
+    while (G > 1 && na / G < 2) G--;                          /* every slab with a neighbour needs two planes (rows) */
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    int prev_dev = -1; cudaGetDevice(&prev_dev);
+    const auto t_start = std::chrono::steady_clock::now();
+    auto since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t).count(); };
+
+    /* phase 1 per slab: scatter + label + export + counts */
+    auto phase1 = [&](int g) -> int {
+        MultiSlab &m = g_multi[g];
+        m.rc = RG_OK; m.err[0] = 0;
+        const int64_t z0 = na * g / G, z1 = na * (g + 1) / G, nzl = z1 - z0;
+        const int lower = g > 0, upper = g < G - 1;
+        if (m.ctx && m.device != devices[g]) {               /* the slot served another device before: start over */
+            cudaSetDevice(m.device);
+            cudaFree(m.buf); cudaFree(m.mask); cudaFree(m.seeds); cudaFree(m.lists); cudaFree(m.counts_d); cudaFree(m.gathered); cudaFree(m.xpar);
+            cudaFreeHost(m.counts_h); cudaStreamDestroy(m.st); rg_ctx_destroy(m.ctx);
+            memset(&m, 0, sizeof m);
+        }
+        MCK(cudaSetDevice(devices[g]));
+        if (!m.ctx) {
+            m.device = devices[g];
+            if (rg_ctx_create(devices[g], &m.ctx) != RG_OK) return multi_fail(m, RG_ERR_CUDA);
+            MCK(cudaStreamCreateWithFlags(&m.st, cudaStreamNonBlocking));
+            MCK(cudaMalloc((void **)&m.counts_d, 16));
+            MCK(cudaHostAlloc((void **)&m.counts_h, 16, cudaHostAllocDefault));
+            for (int o = 0; o < G; o++)                       /* peer copies go over NVLink where the devices can reach each other */
+                if (devices[o] != devices[g]) { int can = 0; cudaDeviceCanAccessPeer(&can, devices[g], devices[o]); if (can) cudaDeviceEnablePeerAccess(devices[o], 0); cudaGetLastError(); }
+        }
+        int rc;
+        if ((rc = multi_room(m, m.buf, m.buf_bytes, (size_t)((nzl + 2) * plane)))) return rc;
+        if ((rc = multi_room(m, m.mask, m.mask_bytes, (size_t)(nzl * plane)))) return rc;
+        const size_t cap = G > 1 ? (size_t)rg_slab_interface_capacity(nx, rows ? nzl : ny, rows ? 1 : nzl) : 1;
+        if (m.cap < cap) { size_t words = 2 * m.cap; if ((rc = multi_room(m, m.lists, words, 2 * cap))) return rc; m.cap = cap; }
+        /* distribute_image + distribute_image_halo: own planes plus the neighbours' boundary planes, from the host image */
+        const int64_t lo = z0 - lower, hi = z1 + upper;
+        if (copy_in(m.ctx, m.buf + (size_t)((lo - z0 + 1) * plane), image + (size_t)(lo * plane), (size_t)((hi - lo) * plane), m.st)) return multi_fail(m, RG_ERR_CUDA);
+        /* add_seeds (region.c:450-490): a seed belongs to the slab that owns its plane (row) */
+        std::vector<int32_t> loc;
+        for (int i = 0; i < nseeds; i++) {
+            const int64_t a = seeds_xyz[3 * i + (rows ? 1 : 2)];
+            if (a >= z0 && a < z1) { int32_t t[3] = { seeds_xyz[3 * i], seeds_xyz[3 * i + 1], seeds_xyz[3 * i + 2] }; t[rows ? 1 : 2] = (int32_t)(a - z0); loc.insert(loc.end(), t, t + 3); }
+        }
+        const int nloc = (int)loc.size() / 3;
+        if ((rc = multi_room(m, m.seeds, m.seeds_cap, (size_t)(nloc > 0 ? 3 * nloc : 3)))) return rc;
+        if (nloc) { MCK(cudaMemcpyAsync(m.seeds, loc.data(), loc.size() * 4, cudaMemcpyHostToDevice, m.st)); MCK(cudaStreamSynchronize(m.st)); }   /* loc dies with this scope */
+        if (rg_slab_label(m.ctx, m.buf + plane, nx, rows ? nzl : ny, rows ? 1 : nzl, lower, upper, nloc ? m.seeds : nullptr, nloc, threshold, m.mask, m.st) != RG_OK)
+            return multi_fail(m, RG_ERR_INTERNAL);
+        MCK(cudaMemsetAsync(m.counts_d, 0, 16, m.st));
+        if (G > 1) {
+            if (lower && rg_slab_export(m.ctx, 0, m.lists, m.counts_d, m.st) != RG_OK) return multi_fail(m, RG_ERR_INTERNAL);
+            if (upper && rg_slab_export(m.ctx, 1, m.lists + m.cap, m.counts_d, m.st) != RG_OK) return multi_fail(m, RG_ERR_INTERNAL);
+        }
+        MCK(cudaMemcpyAsync(m.counts_h, m.counts_d, 16, cudaMemcpyDeviceToHost, m.st));
+        MCK(cudaStreamSynchronize(m.st));
+        return RG_OK;
+    };
+    /* phase 2 per slab: gather every rank's lists, solve the interface union-find redundantly, output pass, gather_region */
+    int64_t counts4[RESOLVE_MAX_RANKS * 4];
+    uint32_t maxn = 0; uint64_t total_nodes = 0;
+    auto phase2 = [&](int g) -> int {
+        MultiSlab &m = g_multi[g];
+        const int64_t z0 = na * g / G, z1 = na * (g + 1) / G, nzl = z1 - z0;
+        MCK(cudaSetDevice(devices[g]));
+        int rc;
+        if (G > 1 && maxn > 0) {
+            if ((rc = multi_room(m, m.gathered, m.gathered_words, (size_t)G * 2 * maxn))) return rc;
+            if ((rc = multi_room(m, m.xpar, m.xpar_words, (size_t)(total_nodes + 2)))) return rc;
+            for (int r = 0; r < G; r++)
+                for (int side = 0; side < 2; side++) {
+                    const size_t n = (size_t)counts4[4 * r + side];
+                    if (!n) continue;
+                    MCK(cudaMemcpyPeerAsync(m.gathered + ((size_t)r * 2 + side) * maxn, devices[g], g_multi[r].lists + (size_t)side * g_multi[r].cap, devices[r], n * 4, m.st));
+                }
+            if (rg_slab_resolve(m.ctx, m.xpar, m.gathered, maxn, counts4, g, G, m.st) != RG_OK) return multi_fail(m, RG_ERR_INTERNAL);
+        }
+        if (rg_slab_finish(m.ctx, m.st) != RG_OK) return multi_fail(m, RG_ERR_INTERNAL);
+        uint8_t *dst = mask_out + (size_t)(z0 * plane);
+        m.ctx->last_h2d_bytes = m.ctx->last_d2h_bytes = 0;
+        if (flags & RG_MULTI_MASK_ZEROED) rc = copy_out_sparse(m.ctx, dst, nx, rows ? nzl : ny, rows ? 1 : nzl, m.st);
+        else rc = copy_out_full(m.ctx, dst, m.mask, (size_t)(nzl * plane), m.st);
+        if (rc) return multi_fail(m, rc);
+        MCK(cudaStreamSynchronize(m.st));
+        if (rg_ctx_status(m.ctx, nullptr) != RG_OK) return multi_fail(m, RG_ERR_INTERNAL);
+        return RG_OK;
+    };
+    auto run_all = [&](const std::function<int(int)> &fn) {
+        std::vector<std::thread> th;
+        for (int g = 1; g < G; g++) th.emplace_back([&, g] { fn(g); });
+        fn(0);
+        for (auto &t : th) t.join();
+        for (int g = 0; g < G; g++) if (g_multi[g].rc) { snprintf(g_err, sizeof g_err, "slab %d (device %d): %s", g, devices[g], g_multi[g].err); return g_multi[g].rc; }
+        return (int)RG_OK;
+    };
+    int rc = run_all(phase1);
+    const float t1 = since(t_start);
+    if (rc == RG_OK) {
+        for (int g = 0; g < G; g++) {
+            const uint32_t *h = g_multi[g].counts_h;
+            counts4[4 * g] = h[0]; counts4[4 * g + 1] = h[1]; counts4[4 * g + 2] = h[2]; counts4[4 * g + 3] = 0;
+            if (h[0] > maxn) maxn = h[0];
+            if (h[1] > maxn) maxn = h[1];
+            total_nodes += h[2];
+        }
+        for (int g = 0; g + 1 < G; g++)
+            if (counts4[4 * g + 1] != counts4[4 * (g + 1)]) rc = fail(RG_ERR_INTERNAL, "interface lists of neighbouring slabs differ in length");
+        if (total_nodes + 2 >= (1ull << 32)) rc = fail(RG_ERR_TOO_LARGE, "too many nodes across slabs for 32-bit vertex ids");
+    }
+    if (rc == RG_OK) rc = run_all(phase2);
+    if (phase_ms) { phase_ms[0] = since(t_start); phase_ms[1] = t1; phase_ms[2] = phase_ms[0] - t1; phase_ms[3] = (float)G; }
+    if (prev_dev >= 0) cudaSetDevice(prev_dev);
+    return rc;
 }

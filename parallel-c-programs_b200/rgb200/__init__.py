@@ -33,6 +33,7 @@ SIGNATURES = {
     "rg_grow": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_grow_sparse": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_host_stats": (_i32, [_vp]),
+    "rg_grow_multi": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp]),
     "rg_ctx_create": (_i32, [_i32, _c.POINTER(_vp)]),
     "rg_ctx_destroy": (None, [_vp]),
     "rg_workspace_bytes": (_i64, [_i64, _i64, _i64, _i32]),

@@ -524,3 +524,44 @@ def test_sparse_output_and_staged_pageable_copies(rg, oracle):
     o3 = np.zeros_like(img)
     assert lib.rg_grow_sparse(img.ctypes.data, 1000, 700, 1, None, 0, 2, o3.ctypes.data) == 0 and not o3.any()
     assert _host_stats(lib)[1] == 0
+
+
+def _grow_multi(lib, img, seeds, T, devices, zeroed=False):
+    img = np.ascontiguousarray(img, np.uint8)
+    nz, ny, nx = (1,) + img.shape if img.ndim == 2 else img.shape
+    seeds = np.ascontiguousarray(np.asarray(seeds, np.int32).reshape(-1, 3))
+    out = np.zeros(img.shape, np.uint8) if zeroed else np.full(img.shape, 9, np.uint8)
+    dev = (ctypes.c_int * len(devices))(*devices)
+    ms = (ctypes.c_float * 4)()
+    rc = lib.rg_grow_multi(img.ctypes.data, nx, ny, nz, seeds.ctypes.data if len(seeds) else None, len(seeds), T, out.ctypes.data,
+                           dev, len(devices), 1 if zeroed else 0, ms)
+    assert rc == 0, lib.rg_last_error()
+    return out, list(ms)
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 5])
+def test_grow_multi_from_c_abi(rg, oracle, G):
+    """rg_grow_multi: one host image scattered over G slabs (here: G slabs on the GPUs this box has, round-robin -- one GPU
+    simply carries several slabs), one interface exchange by peer copies, the mask gathered into the caller's buffer:
+    region.c's distribute -> grow -> gather (region.c:591-597) from one C call.  Volume, image, serpentine; plain and
+    zeroed-mask (sparse copy back) forms."""
+    import torch
+    lib = rg.load_library()
+    ndev = torch.cuda.device_count()
+    devices = [g % ndev for g in range(G)]
+    rng = np.random.default_rng(50 + G)
+    vol = rng.integers(0, 4, size=(70, 90, 200), dtype=np.uint8); vol[5:60, 20:70, 30:170] = 40
+    seeds = [[100, 40, 30], [0, 0, 0], [199, 89, 69], [50, 50, 35]]
+    want = oracle.grow(vol, seeds, 1)
+    got, ms = _grow_multi(lib, vol, seeds, 1, devices)
+    assert (got == want).all() and int(ms[3]) == G
+    got, _ = _grow_multi(lib, vol, seeds, 1, devices, zeroed=True)
+    assert (got == want).all()
+    img, s2, T2 = oracle.synth("c2", 1024, 0x5EED0002)
+    got, _ = _grow_multi(lib, img, s2, T2, devices)
+    assert (got == oracle.grow(img, s2, T2)).all()
+    v3, s3, T3 = oracle.synth("c4", 160, 0x5EED0004)            # the z-serpentine crosses every slab interface many times
+    got, _ = _grow_multi(lib, v3, s3, T3, devices, zeroed=True)
+    assert (got == oracle.grow(v3, s3, T3)).all()
+    got, _ = _grow_multi(lib, v3, np.zeros((0, 3), np.int32), T3, devices)
+    assert not got.any()
