@@ -702,12 +702,12 @@ RG_FN void merge_faces(Exec &ex, const Params &P)
             const uint16_t *ea = ta + here;
             const uint16_t *eb = P.ent + (size_t)nb * C::ENT_MAX + offb;
             /* faces inside a solid list the same pair of nodes hundreds of times: a lane skips a pair it has just united */
-            uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu;
+            uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu, qa = 0xFFFFFFFFu, qb = 0xFFFFFFFFu;      /* the last two pairs: C3's faces alternate corridor / background */
             for (uint32_t i = lane; i < cnt; i += MERGE_LANES) {
                 const uint32_t a = ra.node_base + ea[i], b = rb.node_base + eb[i];
-                if (a == pa && b == pb) continue;
+                if ((a == pa && b == pb) || (a == qa && b == qb)) continue;
                 unite32(P.nparent, a, b);
-                pa = a; pb = b;
+                qa = pa; qb = pb; pa = a; pb = b;
             }
         }
     });

@@ -139,6 +139,7 @@ RG_FN void dense_label_runs(Exec &ex, const Params &P, uint32_t tile, S &s, PT *
             if (m) {
                 const int up = w + C::WX; const uint32_t exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
                 uint32_t n = dedupe(m, exw, exu);
+                if (wx > 0 && (n & 1u)) n &= ~((pey[w - 1] & d.ex[w - 1] & d.ex[up - 1]) >> 31);   /* the pair of runs reaches over from the word before: united there */
                 while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(par, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
             }
         }
@@ -156,10 +157,15 @@ RG_FN void dense_label_runs(Exec &ex, const Params &P, uint32_t tile, S &s, PT *
                 const int up = w + C::WX * C::TY;
                 const uint32_t exw = d.ex[w], lsw = d.ls[w], pre = prefix[w], exu = d.ex[up], lsu = d.ls[up], preu = prefix[up];
                 uint32_t n = dedupe(m, exw, exu);
+                if (r % C::WX > 0 && (n & 1u)) n &= ~((pez[w - 1] & d.ex[w - 1] & d.ex[up - 1]) >> 31);
                 while (n) { const int i = ffs1(n) - 1; n &= n - 1; unite16(par, run_id(exw, lsw, pre, i), run_id(exu, lsu, preu, i)); }
             }
         });
     }
+    ex.sync();
+    /* flatten: every run looks its root up once, all lanes busy; the lookups of the cross-tile edges below -- a handful of
+       threads with eight edges each -- then take one step instead of walking chains on their own */
+    ex.pfor((int)nruns, [&](int i) { const uint32_t r = find16(par, (uint32_t)i); if (r != (uint32_t)i) par[i] = (PT)r; });
     ex.sync();
 
     /* 4. roots that own a cross-tile edge or a seed become nodes */
