@@ -31,9 +31,10 @@
 namespace rg {
 
 enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
-enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_NPLANES = 5, CTR_NDENSE = 6, CTR_WORDS = 8 };
+enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_NPLANES = 5, CTR_NDENSE = 6, CTR_NROWTILES = 7, CTR_WORDS = 8 };
 /* CTR_NCOMPLEX: tiles listed for the full labelling pass; CTR_NDENSE: tiles the in-CTA dense path labelled (rg_dense.h);
-   CTR_NPLANES: link-plane slots handed out (both of those passes keep a tile's planes for pass C) */
+   CTR_NPLANES: link-plane slots handed out (both of those passes keep a tile's planes for pass C);
+   CTR_NROWTILES: tiles of constant rows labelled at row granularity (rg_rows.h) */
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
 /* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
@@ -90,7 +91,8 @@ struct TileRec {                 /* 32 bytes per tile, written by pass A */
     uint32_t node_base;          /* first global node id of this tile */
     uint32_t nnodes;
     uint16_t cnt[6];             /* face-list lengths, order XM XP YM YP ZM ZP */
-    uint16_t uniform;            /* 1: all voxels of the tile are one component (pass C needs no image read) */
+    uint16_t uniform;            /* 1: all voxels of the tile are one component (pass C needs no image read); 2: a tile of constant rows,
+                                    its 2 x TZ row-link words are in its link-plane slot (rg_rows.h) */
     uint16_t has_region;         /* written by the flag pass: 1 = the tile holds region voxels (output-sensitive copies of the mask) */
     uint32_t plane_slot1;        /* 1 + index of the tile's saved link planes (Params::planes), 0 = none */
     uint32_t pad3;
@@ -122,6 +124,7 @@ struct Params {
     uint32_t plane_cap;          /* how many tiles' planes fit */
     int32_t mask_prezeroed;      /* every CTA of the fast labelling pass clears its mask tile while its load is in flight; flag_tiles_all then stores no zeros */
     int32_t force_dense;         /* testing aid (env RG_FORCE_DENSE): the fast labelling pass sends every non-uniform tile down its dense path */
+    int32_t no_rows;             /* testing aid (env RG_NO_ROWS): tiles of constant rows are labelled like any other tile */
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
@@ -749,6 +752,43 @@ struct alignas(128) FloodSmem {
     uint32_t scal[16];
 };
 
+/* pass C for a tile of constant rows (rg_rows.h): the flood runs over TY x TZ row bits -- word z holds the rows of plane z,
+   its links along y are the bits of ly[z] (closed with the same carry trick as a voxel word), lz[z] joins planes z and z+1 */
+template <class C, class Exec>
+RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, FloodSmem<C> &s, const TileRec &rc, int64_t x0, int64_t y0, int64_t z0)
+{
+    uint32_t *ly = s.ex, *lz = s.ex + C::TZ, *M = s.M;
+    const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;
+    ex.pfor(2 * C::TZ, [&](int i) { ly[i] = src[i]; if (i < C::TZ) M[i] = 0; });
+    if (ex.tid() == 0) s.scal[SC_ANY] = 0;
+    ex.sync();
+    ex.pfor((int)rc.nnodes, [&](int i) {
+        const uint32_t g = rc.node_base + (uint32_t)i;
+        if (find32(P.nparent, g) == 0u) {
+            const uint32_t r = (uint32_t)P.nrep[g] / (uint32_t)C::TX;
+            atomic_or(&M[r / C::TY], 1u << (r % C::TY));
+            s.scal[SC_ANY] = 1;
+        }
+    });
+    ex.sync();
+    if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    for (;;) {
+        bool changed = false;
+        ex.pfor(C::TZ, [&](int z) {
+            const uint32_t m = M[z];
+            uint32_t in = m;
+            if (z > 0) in |= M[z - 1] & lz[z - 1];
+            if (z < C::TZ - 1) in |= M[z + 1] & lz[z];
+            if (in) { const uint32_t out = fill_word(in, ly[z]); if (out != m) { M[z] = out; changed = true; } }
+        });
+        if (!ex.sync_or(changed)) break;
+    }
+    ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
+        const int r = it / C::CX, y = r % C::TY, z = r / C::TY;
+        fill_chunk<C>(P, x0, y0, z0, (M[z] >> y) & 1u, it);
+    });
+}
+
 template <class C, class Exec>
 RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s)
 {
@@ -761,6 +801,7 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     const TileRec rc = P.rec[tile];
 
     if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    if (rc.uniform == 2) { tile_pass_c_rows<C>(ex, P, s, rc, x0, y0, z0); return; }
     const bool saved = P.planes && rc.plane_slot1;                  /* the full pass kept this tile's link planes */
     if (saved) {
         const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;

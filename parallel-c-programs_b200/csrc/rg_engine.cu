@@ -639,6 +639,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)d_image & 15) == 0) && (((uintptr_t)d_mask & 15) == 0);
     P.nseeds = nseeds;
     { static int dbg = -1; if (dbg < 0) { const char *e = getenv("RG_DEBUG_STOP"); dbg = e ? atoi(e) : 0; } P.debug_stop = dbg; }
+    { static int nr = -1; if (nr < 0) { const char *e = getenv("RG_NO_ROWS"); nr = e ? atoi(e) : 0; } P.no_rows = nr; }
     { static int fd = -1; if (fd < 0) { const char *e = getenv("RG_FORCE_DENSE"); fd = e ? atoi(e) : 0; } P.force_dense = fd; }   /* testing: every non-uniform tile takes the dense path */
     memset(&c->last_tmap, 0, sizeof c->last_tmap);
     /* the tensor map covers the neighbours' halo planes (volumes) or halo rows (images) as well */
@@ -897,7 +898,7 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
     CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
     CK(cudaStreamSynchronize(c->last_stream));
     /* stats[2]: tiles the walkers did not get through = labelled by the dense path + handed to the full pass */
-    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX] + c->h_status[CTR_NDENSE]; stats[3] = c->h_status[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX] + c->h_status[CTR_NDENSE] + c->h_status[CTR_NROWTILES]; stats[3] = c->h_status[CTR_NFLAGGED]; }
     c->last_full_tiles = c->h_status[CTR_NCOMPLEX];
     if (c->h_status[CTR_STATUS]) {
         if (c->h_status[CTR_STATUS] & ST_NODE_OVERFLOW)
@@ -1277,7 +1278,7 @@ extern "C" int rg_noalloc_status(uint32_t stats[4], void *stream)
     uint32_t h[CTR_WORDS];
     CK(cudaMemcpyAsync(h, src, sizeof h, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CK(cudaStreamSynchronize((cudaStream_t)stream));
-    if (stats) { stats[0] = h[CTR_NODES]; stats[1] = h[CTR_STATUS]; stats[2] = h[CTR_NCOMPLEX] + h[CTR_NDENSE]; stats[3] = h[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = h[CTR_NODES]; stats[1] = h[CTR_STATUS]; stats[2] = h[CTR_NCOMPLEX] + h[CTR_NDENSE] + h[CTR_NROWTILES]; stats[3] = h[CTR_NFLAGGED]; }
     if (h[CTR_STATUS]) {
         snprintf(g_err, sizeof g_err, "engine self-check failed on the no-allocation path: status=0x%x mismatching faces=%u", h[CTR_STATUS], h[CTR_FACE_MISMATCH]);
         return RG_ERR_INTERNAL;

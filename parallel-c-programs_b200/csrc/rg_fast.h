@@ -25,6 +25,7 @@
 #pragma once
 #include "rg_core.h"
 #include "rg_dense.h"
+#include "rg_rows.h"
 
 namespace rg {
 
@@ -256,20 +257,28 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     ex.sync();
     if (P.debug_stop == 1) return;
     /* a tile whose own voxels are all equal is one component with representative 0 (solid interiors) */
-    bool uniform = false;
+    /* ... and a tile whose ROWS are constant is a small grid of rows (rg_rows.h) */
+    bool uniform = false, rows = false;
     if (P.fast16 && P.tmode >= 1) {
         const uint32_t pat = (uint32_t)s.u.img[img_off<C>(0, 0, 0)] * 0x01010101u;
         u32x4 q0 = ld128(&s.u.img[img_off<C>(0, 0, 0)]);
         /* the first 16 voxels decide for almost every tile; all threads read the same bytes, so this branch is uniform */
         if (vx >= 16 && ((q0.x ^ pat) | (q0.y ^ pat) | (q0.z ^ pat) | (q0.w ^ pat)) == 0u) {
-            bool differs = false;
+            bool differs = false, row_differs = false;
             ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
                 int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
                 if (y >= vy || z >= vz || 16 * c >= vx) return;
                 u32x4 q = ld128(&s.u.img[img_off<C>(16 * c, y, z)]);
-                if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) differs = true;
+                if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) {
+                    differs = true;
+                    const uint32_t rp = (uint32_t)s.u.img[img_off<C>(0, y, z)] * 0x01010101u;
+                    if ((q.x ^ rp) | (q.y ^ rp) | (q.z ^ rp) | (q.w ^ rp)) row_differs = true;
+                }
             });
-            uniform = !ex.sync_or(differs);
+            if (!ex.sync_or(row_differs)) {
+                uniform = !ex.sync_or(differs);
+                rows = !uniform && RowsCfg<C>::OK && vx == C::TX && P.planes && !P.no_rows && !P.force_dense;
+            }
         }
     }
     build_face_masks<C>(ex, P, s.u.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
@@ -284,6 +293,19 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     const uint32_t base = fast_node_base(tile);
     uint16_t *ent = P.ent + (size_t)tile * C::ENT_MAX;
     uint32_t nnodes;
+    if (rows) {
+        /* needs a link-plane slot for its row links; without one (more such tiles than slots) it is labelled like any other tile */
+        if (ex.tid() == 0) {
+            const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u);
+            s.scal[SC_PLANE1] = slot < P.plane_cap ? slot + 1u : 0u;
+        }
+        ex.sync();
+        rows = s.scal[SC_PLANE1] != 0;
+    }
+    if (rows) {
+        if (RowsCfg<C>::OK) tile_label_rows<C>(ex, P, tile, s, vy, vz);
+        return;
+    }
     if (uniform) {
         ex.pfor((int)etot, [&](int e) { ent[e] = 0; });
         nnodes = (etot || seeded) ? 1u : 0u;
@@ -417,7 +439,7 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
         },
         [&](uint32_t tile, uint32_t lane, bool mine) {
             if (lane == 0) P.rec[tile].has_region = mine ? 1 : 0;
-            if (mine && !P.rec[tile].uniform) {
+            if (mine && P.rec[tile].uniform != 1) {
                 if (lane == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
                 return;
             }

@@ -59,7 +59,10 @@ struct HostExec {
 static int g_force_full = 0;
 static int g_no_planes = 0;      /* 1: label every tile with the full pass (fast pass off) */
 static int g_force_dense = 0;    /* 1: every non-uniform tile takes the dense path of the fast pass */
-static uint32_t g_last_dense = 0, g_last_full = 0;
+static int g_no_rows = 0;        /* 1: tiles of constant rows are labelled like any other tile */
+static uint32_t g_last_dense = 0, g_last_full = 0, g_last_rows = 0;
+extern "C" void emu_no_rows(int v) { g_no_rows = v; }
+extern "C" uint32_t emu_last_rows(void) { return g_last_rows; }
 extern "C" void emu_force_dense(int v) { g_force_dense = v; }
 extern "C" uint32_t emu_last_dense(void) { return g_last_dense; }
 extern "C" uint32_t emu_last_full(void) { return g_last_full; }
@@ -83,6 +86,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
     P.mask_prezeroed = g_force_full ? 0 : 1;
     P.force_dense = g_force_dense;
+    P.no_rows = g_no_rows;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);
     size_t ntiles = (size_t)P.ntx * P.nty * P.ntz;
     size_t cap = 1 + ntiles * ((size_t)C::ENT_MAX + FAST_NODE_SLOTS) + (size_t)nseeds;
@@ -136,8 +140,8 @@ static int emu_grow_t(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, 
     emu_label<C>(E);
     emu_finish<C>(E);
     uint32_t real_nodes = 0; for (const TileRec &r : E.rec) real_nodes += r.nnodes;
-    if (stats) { stats[0] = real_nodes; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX] + E.counters[CTR_NDENSE]; stats[3] = (uint32_t)E.rec.size(); }
-    g_last_dense = E.counters[CTR_NDENSE]; g_last_full = E.counters[CTR_NCOMPLEX];
+    if (stats) { stats[0] = real_nodes; stats[1] = E.counters[CTR_STATUS]; stats[2] = E.counters[CTR_NCOMPLEX] + E.counters[CTR_NDENSE] + E.counters[CTR_NROWTILES]; stats[3] = (uint32_t)E.rec.size(); }
+    g_last_dense = E.counters[CTR_NDENSE]; g_last_full = E.counters[CTR_NCOMPLEX]; g_last_rows = E.counters[CTR_NROWTILES];
     return E.counters[CTR_STATUS] ? -4 : 0;
 }
 
@@ -329,7 +333,7 @@ extern "C" int rg_slab_resolve_packed(void *cv, uint32_t *xpar, uint32_t xpar_ca
 extern "C" int rg_ctx_status(void *cv, uint32_t *stats)
 {
     EmuCtx *c = (EmuCtx *)cv;
-    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX] + c->E.counters[CTR_NDENSE]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX] + c->E.counters[CTR_NDENSE] + c->E.counters[CTR_NROWTILES]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
     return c->E.counters[CTR_STATUS] ? -4 : 0;
 }
 extern "C" int rg_slab_finish(void *cv, void *)

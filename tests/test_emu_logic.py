@@ -303,3 +303,37 @@ def test_emu_dense_path_overflow_goes_to_the_full_pass(emu, oracle):
         emu.emu_force_dense(0)
     assert (got == want).all()
     assert emu.emu_last_full() >= 1 and emu.emu_last_dense() >= 1, (emu.emu_last_full(), emu.emu_last_dense())
+
+
+@pytest.mark.parametrize("cfg", [0, 1, 2])
+def test_emu_row_tiles(emu, oracle, cfg):
+    """tiles whose rows are constant are labelled as a grid of rows (rg_rows.h) and flooded row-wise in pass C; their
+    neighbours are noise tiles, uniform tiles and ragged tiles on the ordinary paths; with no link-plane slot left (the
+    emulator keeps room for every second tile) a row tile is labelled like any other"""
+    emu.emu_last_rows.restype = ctypes.c_uint32
+    rng = np.random.default_rng(123 + cfg)
+    nz, ny, nx = (40, 70, 256) if cfg == 0 else (14, 26, 208)
+    rowval = rng.integers(0, 3, size=(nz, ny, 1), dtype=np.uint8) * 50           # every row constant, neighbours often equal
+    img = np.broadcast_to(rowval, (nz, ny, nx)).copy()
+    img[:, :, nx // 2: nx // 2 + 40] = rng.integers(0, 4, size=(nz, ny, 40))      # a noise band: those tiles are not row tiles
+    img[2:8, 3:9, :] = 200                                                        # a slab of equal rows
+    seeds = [[0, 0, 0], [nx - 1, ny - 1, nz - 1], [5, 5, 5], [nx // 2 + 3, 7, 3], [10, ny // 2, nz // 2]]
+    for T in (1, 60, 300):
+        want = oracle.grow(img, seeds, T)
+        got, st = run_emu(emu, cfg, img, seeds, T)
+        assert (got == want).all(), (cfg, T)
+        if T == 1:
+            assert emu.emu_last_rows() > 0
+        emu.emu_no_rows(1)
+        try:
+            got2, _ = run_emu(emu, cfg, img, seeds, T)
+        finally:
+            emu.emu_no_rows(0)
+        assert (got2 == want).all() and emu.emu_last_rows() == 0
+        if nz >= 6:
+            got3, _ = run_emu(emu, cfg, img, seeds, T, slabs=3)
+            assert (got3 == want).all(), ("slabs", cfg, T)
+    # the serpentine: every tile column but the two with the turns is made of constant rows
+    img3, s3, T3 = oracle.synth("c3", 192 if cfg != 1 else 96)
+    got, _ = run_emu(emu, cfg, img3, s3, T3)
+    assert (got == oracle.grow(img3, s3, T3)).all() and emu.emu_last_rows() > 0

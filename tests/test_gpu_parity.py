@@ -565,3 +565,22 @@ def test_grow_multi_from_c_abi(rg, oracle, G):
     assert (got == oracle.grow(v3, s3, T3)).all()
     got, _ = _grow_multi(lib, v3, np.zeros((0, 3), np.int32), T3, devices)
     assert not got.any()
+
+
+def test_row_tiles_on_gpu(rg, ctx, oracle, monkeypatch):
+    """tiles of constant rows (rg_rows.h) next to noise, uniform and ragged tiles, seeds in every kind; same bytes as the
+    oracle, and as the run with the row path switched off"""
+    rng = np.random.default_rng(8)
+    nz, ny, nx = 50, 100, 320
+    rowval = rng.integers(0, 3, size=(nz, ny, 1), dtype=np.uint8) * 70
+    img = np.broadcast_to(rowval, (nz, ny, nx)).copy()
+    img[:, :, 128:192] = rng.integers(0, 5, size=(nz, ny, 64))
+    img[5:40, 10:90, 200:320] = 9
+    seeds = [[0, 0, 0], [319, 99, 49], [150, 50, 25], [250, 50, 20], [10, 70, 33]]
+    for T in (1, 71, 256):
+        want = oracle.grow(img, seeds, T)
+        assert (dev_grow(rg, ctx, img, seeds, T) == want).all(), T
+    img3, s3, T3 = oracle.synth("c3", 256)
+    want3 = oracle.grow(img3, s3, T3)
+    got3 = dev_grow(rg, ctx, img3, s3, T3)
+    assert (got3 == want3).all()
