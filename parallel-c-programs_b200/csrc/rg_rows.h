@@ -57,34 +57,32 @@ RG_FN void tile_label_rows(Exec &ex, const Params &P, uint32_t tile, S &s, int v
         const int y = r % C::TY, z = r / C::TY;
         val[r] = (y < vy && z < vz) ? s.u.img[img_off<C>(0, y, z)] : (uint8_t)0;
         par[r] = (uint16_t)r;
+        if (r < C::TZ) { ly[r] = 0; lz[r] = 0; open[r] = 0; seeded[r] = 0; }
     });
     ex.sync();
-    ex.pfor(2 * C::TZ, [&](int it) {
-        const int z = it % C::TZ, dir = it / C::TZ;
-        uint32_t w = 0;
-        if (z < vz)
-            for (int y = 0; y < vy; y++) {
-                const int r = z * C::TY + y;
-                const bool has = dir ? (z + 1 < vz) : (y + 1 < vy);
-                if (has && similar1(val[r], val[dir ? r + C::TY : r + 1], tmode, t4)) w |= 1u << y;
-            }
-        (dir ? lz : ly)[z] = w;
-        if (!dir) { open[z] = 0; seeded[z] = 0; }
+    ex.pfor(NROWS, [&](int r) {
+        const int y = r % C::TY, z = r / C::TY;
+        if (y >= vy || z >= vz) return;
+        if (y + 1 < vy && similar1(val[r], val[r + 1], tmode, t4)) atomic_or(&ly[z], 1u << y);
+        if (z + 1 < vz && similar1(val[r], val[r + C::TY], tmode, t4)) atomic_or(&lz[z], 1u << y);
     });
     ex.sync();
-    /* one thread per plane walks its rows, then one per row position walks the planes: a thread finds the tree it has just
-       extended already flat */
-    ex.pfor(C::TZ, [&](int z) {
-        uint32_t m = ly[z];
-        while (m) { const int y = ffs1(m) - 1; m &= m - 1; unite16(par, (uint32_t)(z * C::TY + y), (uint32_t)(z * C::TY + y + 1)); }
+    /* Rows of a plane that are linked in y form runs, exactly like voxels of a word linked in x: a run is named by its first
+       row (bit tricks, no union), and planes are joined by one union per pair of overlapping runs -- all of them at once. */
+    auto run_row = [&](int z, int y) { return (uint32_t)(z * C::TY) + (run_start(ly[z], 0, y) & 31u); };
+    ex.pfor(NROWS, [&](int r) {
+        const int y = r % C::TY, z = r / C::TY;
+        if (z + 1 >= C::TZ) return;
+        const uint32_t n = dedupe(lz[z], ly[z], ly[z + 1]);
+        if ((n >> y) & 1u) unite16(par, run_row(z, y), run_row(z + 1, y));
     });
     ex.sync();
-    ex.pfor(C::TY, [&](int y) {
-        for (int z = 0; z + 1 < C::TZ; z++)
-            if ((lz[z] >> y) & 1u) unite16(par, (uint32_t)(z * C::TY + y), (uint32_t)((z + 1) * C::TY + y));
+    /* root of every row, flat */
+    ex.pfor(NROWS, [&](int r) {
+        const int y = r % C::TY, z = r / C::TY;
+        const uint32_t q = find16(par, run_row(z, y));
+        if (q != (uint32_t)r) par[r] = (uint16_t)q;
     });
-    ex.sync();
-    ex.pfor(NROWS, [&](int r) { const uint32_t q = find16(par, (uint32_t)r); if (q != (uint32_t)r) par[r] = (uint16_t)q; });
     /* the link words are all pass C needs */
     {
         uint32_t *keep = P.planes + (size_t)(s.scal[SC_PLANE1] - 1u) * 3 * C::NW;
