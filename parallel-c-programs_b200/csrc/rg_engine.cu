@@ -181,7 +181,7 @@ struct DevExec {
 };
 
 /* ------------------------------------------------------------------ kernels */
-#define RG_THREADS 512          /* full tile passes: 2 CTAs/SM (105 KB smem each) */
+#define RG_THREADS 512          /* full labelling pass: 2 CTAs/SM (104 KB smem each) */
 #ifndef RG_FAST_THREADS
 #define RG_FAST_THREADS 256     /* fast labelling pass: 4 CTAs/SM (56 KB smem each, lean staging layout) */
 #endif

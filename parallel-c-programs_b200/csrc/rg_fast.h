@@ -6,15 +6,16 @@
  * the inputs the reference generates (rand()%20 noise around a few solids, raycast.cu:114-144)
  * almost every component is a handful of voxels and only ~1 % of them reach a tile face.  So:
  *
- *   tile_pass_a_fast  one CTA per tile, 68 KB smem (3 CTAs/SM): stage the tile with TMA and, while the load
- *                     is in flight, clear the tile's part of the mask; compute edge words ONLY on the six
- *                     face layers, then let one thread per cross-tile edge (and per seed) walk its
+ *   tile_pass_a_fast  one CTA per tile, 57 KB smem (4 CTAs/SM, lean staging layout): stage the tile with TMA and, while
+ *                     the load is in flight, clear the tile's part of the mask with bulk stores; compute edge words ONLY
+ *                     on the six face layers, then let one thread per cross-tile edge (and per seed) walk its
  *                     component directly on the staged bytes, at most WALK_MAX voxels.  The walk returns
- *                     the component's smallest voxel index -- the same representative the union-find of
- *                     the full pass produces -- and a shared-memory hash table turns representatives
- *                     into dense node ids, so nodes and face lists come out as in rg_core.h.  A tile in
- *                     which any walk overflows (a solid's surface, a corridor ...) is appended to a work
- *                     list and labelled by the full pass instead; nothing but zeros is written for it here.
+ *                     the component's smallest voxel index -- the same representative the union-find paths
+ *                     produce -- and a shared-memory hash table turns representatives
+ *                     into dense node ids, so nodes and face lists come out as in rg_core.h.  A tile whose voxels are all
+ *                     equal is one component; a tile of constant rows is labelled as a grid of rows (rg_rows.h); a tile
+ *                     in which a walk overflows (a solid's surface, a corridor ...) is labelled on the spot by the dense
+ *                     path (rg_dense.h).  Only what overflows even that goes to the work list of the full pass.
  *   flag_tiles_all    one warp per tile, no smem: decides whether any node of the tile ended up in the
  *                     region (root == node 0).  Uniform region tiles are filled with ones, the other region
  *                     tiles are appended to the pass C work list; empty tiles were cleared by the fast pass.
