@@ -31,10 +31,11 @@
 namespace rg {
 
 enum { F_XM = 0, F_XP = 1, F_YM = 2, F_YP = 3, F_ZM = 4, F_ZP = 5 };
-enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_NPLANES = 5, CTR_NDENSE = 6, CTR_NROWTILES = 7, CTR_WORDS = 8 };
+enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, CTR_NFLAGGED = 4, CTR_NPLANES = 5, CTR_NDENSE = 6, CTR_NROWTILES = 7, CTR_NROWOUT = 8, CTR_WORDS = 16 };
 /* CTR_NCOMPLEX: tiles listed for the full labelling pass; CTR_NDENSE: tiles the in-CTA dense path labelled (rg_dense.h);
    CTR_NPLANES: link-plane slots handed out (both of those passes keep a tile's planes for pass C);
-   CTR_NROWTILES: tiles of constant rows labelled at row granularity (rg_rows.h) */
+   CTR_NROWTILES: tiles of constant rows labelled at row granularity (rg_rows.h); CTR_NROWOUT: those of them that hold region
+   voxels (listed from the END of flag_list downwards for the row output kernel) */
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
 /* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
@@ -752,10 +753,18 @@ struct alignas(128) FloodSmem {
     uint32_t scal[16];
 };
 
+/* all the shared memory the output of a row tile needs (k_rows_out: many light CTAs per SM) */
+template <class C>
+struct RowsOutSmem {
+    uint32_t ex[2 * C::TZ + 2];
+    uint32_t M[C::TZ + 1];
+    uint32_t scal[16];
+};
+
 /* pass C for a tile of constant rows (rg_rows.h): the flood runs over TY x TZ row bits -- word z holds the rows of plane z,
    its links along y are the bits of ly[z] (closed with the same carry trick as a voxel word), lz[z] joins planes z and z+1 */
-template <class C, class Exec>
-RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, FloodSmem<C> &s, const TileRec &rc, int64_t x0, int64_t y0, int64_t z0)
+template <class C, class S, class Exec>
+RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, const TileRec &rc, int64_t x0, int64_t y0, int64_t z0)
 {
     uint32_t *ly = s.ex, *lz = s.ex + C::TZ, *M = s.M;
     const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;

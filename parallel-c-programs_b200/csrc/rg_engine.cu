@@ -253,6 +253,17 @@ __global__ void __launch_bounds__(RG_PASSC_THREADS, 3) k_pass_c(const Params P, 
     pass_c_list<L>(ex, P, s);
 }
 
+/* pass C for tiles of constant rows: no staging, a few words of shared memory, many CTAs per SM */
+#define RG_ROWS_THREADS 128
+#define RG_ROWS_CTAS (148 * 12)
+template <class C>
+__global__ void __launch_bounds__(RG_ROWS_THREADS) k_rows_out(const Params P)
+{
+    __shared__ RowsOutSmem<C> s;
+    DevExec<RG_ROWS_THREADS> ex;
+    rows_out_list<C>(ex, P, s);
+}
+
 template <class C>
 __global__ void __launch_bounds__(256) k_region_boxes(const Params P, int32_t *out)
 {
@@ -705,6 +716,7 @@ static int launch_finish(rg_ctx *c, cudaStream_t st)
     } else {
         k_flag_tiles<Cfg3D><<<flag_blocks(c->last_ntiles), RG_FLAG_THREADS, 0, st>>>(c->last_P);
         if (c->profile) cudaEventRecord(c->ev[5], st);
+        if (c->last_P.planes) k_rows_out<Cfg3D><<<RG_ROWS_CTAS, RG_ROWS_THREADS, 0, st>>>(c->last_P);      /* row tiles exist only with link-plane slots */
         k_pass_c<Cfg3D><<<RG_PASSC_CTAS, RG_PASSC_THREADS, sizeof(FloodSmem<LeanOf<Cfg3D>::type>), st>>>(c->last_P, c->last_tmap_fast);
     }
     if (c->profile) cudaEventRecord(c->ev[6], st);
@@ -898,7 +910,7 @@ extern "C" int rg_ctx_status(rg_ctx *c, uint32_t stats[4])
     CK(cudaMemcpyAsync(c->h_status, c->last_counters, CTR_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->last_stream));
     CK(cudaStreamSynchronize(c->last_stream));
     /* stats[2]: tiles the walkers did not get through = labelled by the dense path + handed to the full pass */
-    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX] + c->h_status[CTR_NDENSE] + c->h_status[CTR_NROWTILES]; stats[3] = c->h_status[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = c->h_status[CTR_NODES]; stats[1] = c->h_status[CTR_STATUS]; stats[2] = c->h_status[CTR_NCOMPLEX] + c->h_status[CTR_NDENSE] + c->h_status[CTR_NROWTILES]; stats[3] = c->h_status[CTR_NFLAGGED] + c->h_status[CTR_NROWOUT]; }
     c->last_full_tiles = c->h_status[CTR_NCOMPLEX];
     if (c->h_status[CTR_STATUS]) {
         if (c->h_status[CTR_STATUS] & ST_NODE_OVERFLOW)
@@ -1278,7 +1290,7 @@ extern "C" int rg_noalloc_status(uint32_t stats[4], void *stream)
     uint32_t h[CTR_WORDS];
     CK(cudaMemcpyAsync(h, src, sizeof h, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     CK(cudaStreamSynchronize((cudaStream_t)stream));
-    if (stats) { stats[0] = h[CTR_NODES]; stats[1] = h[CTR_STATUS]; stats[2] = h[CTR_NCOMPLEX] + h[CTR_NDENSE] + h[CTR_NROWTILES]; stats[3] = h[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = h[CTR_NODES]; stats[1] = h[CTR_STATUS]; stats[2] = h[CTR_NCOMPLEX] + h[CTR_NDENSE] + h[CTR_NROWTILES]; stats[3] = h[CTR_NFLAGGED] + h[CTR_NROWOUT]; }
     if (h[CTR_STATUS]) {
         snprintf(g_err, sizeof g_err, "engine self-check failed on the no-allocation path: status=0x%x mismatching faces=%u", h[CTR_STATUS], h[CTR_FACE_MISMATCH]);
         return RG_ERR_INTERNAL;

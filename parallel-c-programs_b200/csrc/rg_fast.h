@@ -259,7 +259,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     if (P.debug_stop == 1) return;
     /* a tile whose own voxels are all equal is one component with representative 0 (solid interiors) */
     /* ... and a tile whose ROWS are constant is a small grid of rows (rg_rows.h) */
-    bool uniform = false, rows = false;
+    bool uniform = false, rows = false, structured = false;
     if (P.fast16 && P.tmode >= 1) {
         const uint32_t pat = (uint32_t)s.u.img[img_off<C>(0, 0, 0)] * 0x01010101u;
         u32x4 q0 = ld128(&s.u.img[img_off<C>(0, 0, 0)]);
@@ -280,6 +280,10 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
                 uniform = !ex.sync_or(differs);
                 rows = !uniform && RowsCfg<C>::OK && vx == C::TX && P.planes && !P.no_rows && !P.force_dense;
             }
+            /* sixteen equal voxels in a row do not happen in noise: the tile starts inside a solid or a corridor and is neither
+               uniform nor made of rows, i.e. it holds a surface or a turn -- the walkers would give up on it, so it goes straight
+               to the dense path */
+            structured = !uniform && !rows;
         }
     }
     build_face_masks<C>(ex, P, s.u.img, s.v.e.xr, s.v.e.u.f.fmask, x0, y0, z0);
@@ -312,7 +316,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         nnodes = (etot || seeded) ? 1u : 0u;
         if (ex.tid() == 0 && nnodes) { P.nparent[base] = seeded ? 0u : base; P.nrep[base] = 0; }
     } else {
-        if (etot > (uint32_t)FAST_ENT_MAX || P.force_dense) {                            /* same total in every thread */
+        if (etot > (uint32_t)FAST_ENT_MAX || structured || P.force_dense) {              /* same decision in every thread */
             /* too many cross-tile edges for the walkers: label the tile from the staged bytes (rg_dense.h) */
             if (!tile_label_dense<C>(ex, P, tile, s, x0, vy, vz)) fast_give_up<C>(ex, P, tile);
             return;
@@ -440,6 +444,10 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
         },
         [&](uint32_t tile, uint32_t lane, bool mine) {
             if (lane == 0) P.rec[tile].has_region = mine ? 1 : 0;
+            if (mine && P.rec[tile].uniform == 2) {                  /* a row tile: the light output kernel, listed from the end */
+                if (lane == 0) P.flag_list[ntiles - 1u - atomic_add(&P.counters[CTR_NROWOUT], 1u)] = tile;
+                return;
+            }
             if (mine && P.rec[tile].uniform != 1) {
                 if (lane == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
                 return;
@@ -449,6 +457,19 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
             const int64_t x0 = (int64_t)tx * C::TX, y0 = (int64_t)ty * C::TY, z0 = (int64_t)tz * C::TZ;
             for (int it = (int)lane; it < C::TZ * C::TY * C::CX; it += FLAG_LANES) fill_chunk<C>(P, x0, y0, z0, mine ? 1u : 0u, it);
         });
+}
+
+/* the region tiles of constant rows: 2 x TZ link words in, whole rows of mask bytes out */
+template <class C, class Exec>
+RG_FN void rows_out_list(Exec &ex, const Params &P, RowsOutSmem<C> &s)
+{
+    const uint32_t n = P.counters[CTR_NROWOUT], ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
+    for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
+        const uint32_t tile = P.flag_list[ntiles - 1u - i];
+        int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
+        tile_pass_c_rows<C>(ex, P, s, P.rec[tile], (int64_t)tx * C::TX, (int64_t)ty * C::TY, (int64_t)tz * C::TZ);
+        ex.sync();
+    }
 }
 
 template <class C, class Exec>

@@ -126,6 +126,8 @@ template <class C> static void emu_finish(EmuState &E)
     typedef typename LeanOf<C>::type LC;                             /* pass C stages in the lean layout, as the kernel does */
     FloodSmem<LC> *s = (FloodSmem<LC> *)aligned_alloc(128, (sizeof(FloodSmem<LC>) + 127) / 128 * 128);
     flag_tiles_all<C>(ex, P);
+    RowsOutSmem<LC> rs; memset(&rs, 0x5A, sizeof rs);
+    rows_out_list<LC>(ex, P, rs);
     memset(s, 0x5A, sizeof *s);
     pass_c_list<LC>(ex, P, *s);
     free(s);
@@ -333,7 +335,7 @@ extern "C" int rg_slab_resolve_packed(void *cv, uint32_t *xpar, uint32_t xpar_ca
 extern "C" int rg_ctx_status(void *cv, uint32_t *stats)
 {
     EmuCtx *c = (EmuCtx *)cv;
-    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX] + c->E.counters[CTR_NDENSE] + c->E.counters[CTR_NROWTILES]; stats[3] = c->E.counters[CTR_NFLAGGED]; }
+    if (stats) { stats[0] = c->E.counters[CTR_NODES]; stats[1] = c->E.counters[CTR_STATUS]; stats[2] = c->E.counters[CTR_NCOMPLEX] + c->E.counters[CTR_NDENSE] + c->E.counters[CTR_NROWTILES]; stats[3] = c->E.counters[CTR_NFLAGGED] + c->E.counters[CTR_NROWOUT]; }
     return c->E.counters[CTR_STATUS] ? -4 : 0;
 }
 extern "C" int rg_slab_finish(void *cv, void *)
