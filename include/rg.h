@@ -165,6 +165,29 @@ const char *rg_last_error(void);
 int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds_xyz, int nseeds,
                   int threshold, uint8_t *mask_out, const int *devices, int ndev, int flags, float *phase_ms);
 
+/* The same for an IMAGE over a rows x cols grid of blocks, the reference's Cartesian process grid (region.c:537-548: MPI_Dims_create /
+ * MPI_Cart_create; distribute_image :106-143; the four-border exchange() :250-353; gather_region :391-432): block (i, j) =
+ * rows [h*i/rows, h*(i+1)/rows) x columns [x_j, x_(j+1)), column cuts on multiples of 128 pixels, devices[i * cols + j] its GPU
+ * (a GPU may be named several times).  No halo travels: each block labels itself with its seams open (every seam pixel becomes an
+ * interface entry), and the exchange unites two components where the two pixels facing each other across a seam are similar.
+ * Same result as rg_grow.  An image too narrow for `cols` blocks of at least 128 columns gets fewer; phase_ms[3] = 1000 * rows used +
+ * columns used.  flags: reserved (0). */
+int rg_grow_multi_grid(const uint8_t *image, int64_t width, int64_t height, const int32_t *seeds_xyz, int nseeds, int threshold,
+                       uint8_t *mask_out, const int *devices, int rows, int cols, int flags, float *phase_ms);
+
+/* The phases rg_grow_multi_grid is built from, for a host with one process per GPU (MPI ranks on a Cartesian grid, as region.c):
+ * rg_block_label labels a device-resident block whose borders in `open_sides` (bit 0 / 1 / 2 / 3 = -x / +x / -y / +y) are seams
+ * to other blocks -- a block with a +x seam must be a multiple of 128 pixels wide --; rg_block_export lists, for every pixel of
+ * one such border in order, the local root of its component and its value; after moving the lists (MPI / NCCL / peer copies) every
+ * rank runs rg_slab_resolve_init on each list with its block's vertex offset, rg_block_resolve_union on each seam (two lists that
+ * face each other: entry i against entry i, united where |value_a - value_b| < threshold), rg_slab_resolve_apply on its own lists,
+ * then rg_slab_finish.  Replaces exchange() / add_halo_to_stack() / finished() of region.c:250-387, 435-440 for a 2-D grid. */
+int rg_block_label(rg_ctx *ctx, const uint8_t *d_block, int64_t width, int64_t height, int open_sides, const int32_t *d_seeds_xyz, int nseeds,
+                   int threshold, uint8_t *d_mask_block, void *stream);
+int rg_block_export(rg_ctx *ctx, int side, uint32_t *d_roots, uint8_t *d_values, void *stream);
+int rg_block_resolve_union(rg_ctx *ctx, uint32_t *d_xpar, const uint32_t *d_roots_a, uint32_t off_a, const uint8_t *d_values_a,
+                           const uint32_t *d_roots_b, uint32_t off_b, const uint8_t *d_values_b, uint32_t n, int threshold, void *stream);
+
 /* ---- z-slab (multi-GPU) phases ------------------------------------------------------------- */
 /* Together these replace the distributed half of 2-mpi-region-growing/region.c -- exchange()
  * (:250-353), add_halo_to_stack() (:355-387), finished() (:435-440) and the static image-halo

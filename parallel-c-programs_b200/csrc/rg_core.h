@@ -106,6 +106,9 @@ struct Params {
     int32_t ntx, nty, ntz;
     int32_t lo_ext, hi_ext;      /* slab has a neighbour slab below / above (multi-GPU) along the slab axis:
                                     z for volumes (tiles with a z halo), y for images -- see ext_ylo() ... */
+    uint32_t open;               /* images cut into blocks (rows x columns over several GPUs): bit 0 / 1 / 2 / 3 = the block's -x / +x / -y / +y
+                                    border is a seam to another block.  Every pixel on such a border becomes a cross-tile edge (no halo is
+                                    read, nothing is compared): the exchange itself tests the pixel pairs across the seam (rg_slab_core.h) */
     int32_t tmode;               /* 0: T <= 0 (no edges)  1: 1..255  2: T >= 256 (all edges) */
     uint32_t t4;                 /* T replicated into 4 bytes */
     uint32_t thr;                /* scalar form: similar <=> |a-b| < thr  (0, T or 256) */

@@ -15,6 +15,7 @@
 #include <thread>
 #include <vector>
 #include <functional>
+#include <algorithm>
 #include <chrono>
 
 #include "rg_core.h"
@@ -329,6 +330,18 @@ __global__ void __launch_bounds__(128) k_export_entries(const Params P, int side
     if (blockIdx.x == 0 && threadIdx.x == 0) counts3[2] = P.counters[CTR_NODES];
     export_entries<C>(ex, P, side, tile_off, out_roots, cap);
 }
+template <class C>
+__global__ void __launch_bounds__(256) k_export_border(const Params P, int side, uint32_t *roots, uint8_t *vals)
+{
+    DevExec<256> ex;
+    export_border<C>(ex, P, side, roots, vals);
+}
+__global__ void __launch_bounds__(256) k_resolve_union_seam(uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint8_t *va,
+                                                            const uint32_t *b, uint32_t offb, const uint8_t *vb, uint32_t n, uint32_t thr)
+{
+    DevExec<256> ex;
+    resolve_union_seam(ex, xpar, a, offa, va, b, offb, vb, n, thr);
+}
 __global__ void k_resolve_prepare(const Params P, const uint32_t *packed_all, uint32_t stride_words, uint32_t cap, uint32_t xpar_cap,
                                   uint32_t rank, uint32_t world, ResolveArgs *A, uint32_t *xpar)
 {
@@ -418,6 +431,7 @@ struct rg_ctx {
     uint32_t *last_counters;                   /* device counters of the last call */
     cudaStream_t last_stream;
     bool attr_set;
+    uint32_t next_open;                        /* Params::open of the next label pass (set by rg_block_label, consumed once) */
     bool may_grow;                             /* the context owns its scratch and may enlarge it (not the noalloc view) */
     bool worst_case_layout;                    /* size the node space for the worst case whatever RG_NODE_BUDGET says (the noalloc view) */
     size_t tail_refused;                       /* smallest size for which the optional link-plane tail did not fit (0 = never failed) */
@@ -644,6 +658,7 @@ static int launch_label(rg_ctx *c, const Layout &L, const uint8_t *d_image, int6
     P.image = d_image; P.mask = d_mask; P.nx = nx; P.ny = ny; P.nz = nz;
     P.ntx = L.ntx; P.nty = L.nty; P.ntz = L.ntz;
     P.lo_ext = lo_ext; P.hi_ext = hi_ext;
+    P.open = c->next_open; c->next_open = 0;
     P.tmode = threshold <= 0 ? 0 : threshold >= 256 ? 2 : 1;
     P.t4 = (uint32_t)(threshold & 0xFF) * 0x01010101u;
     P.thr = threshold <= 0 ? 0u : threshold >= 256 ? 256u : (uint32_t)threshold;
@@ -885,6 +900,41 @@ extern "C" int rg_slab_resolve_packed(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar
     k_resolve_init_packed<<<blocks_for((uint32_t)world * 2u * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
     k_resolve_union_packed<<<blocks_for((uint32_t)(world - 1) * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
     k_resolve_apply_packed<<<blocks_for(2u * cap), 256, 0, st>>>(c->last_P, d_xpar, d_packed_all, cap, c->d_rargs);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+/* ---- blocks of an image (rows x columns) ---- */
+extern "C" int rg_block_label(rg_ctx *c, const uint8_t *d_block, int64_t w, int64_t h, int open_sides, const int32_t *d_seeds_xyz, int nseeds,
+                              int threshold, uint8_t *d_mask_block, void *stream)
+{
+    if (!c || w < 1 || h < 1 || (open_sides & ~15)) return fail(RG_ERR_ARG, "bad argument");
+    if ((open_sides & 2) && w % Cfg2D::TX) return fail(RG_ERR_ARG, "a block with a seam on its +x border must be a multiple of 128 pixels wide");
+    c->next_open = (uint32_t)open_sides;
+    int rc = label_device_impl(c, d_block, w, h, 1, 0, 0, d_seeds_xyz, nseeds, threshold, d_mask_block, stream);
+    c->next_open = 0;
+    return rc;
+}
+
+extern "C" int rg_block_export(rg_ctx *c, int side, uint32_t *d_roots, uint8_t *d_values, void *stream)
+{
+    if (!c || !c->have_last || !c->last_is2d || side < 0 || side > 3 || !d_roots || !d_values) return fail(RG_ERR_ARG, "bad argument");
+    if (!(c->last_P.open & (1u << side))) return fail(RG_ERR_ARG, "that border of the block was not labelled as a seam");
+    ON_DEVICE(c->device);
+    const int64_t n = side < 2 ? c->last_P.ny : c->last_P.nx;
+    k_export_border<Cfg2D><<<blocks_for((uint32_t)n), 256, 0, (cudaStream_t)stream>>>(c->last_P, side, d_roots, d_values);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+extern "C" int rg_block_resolve_union(rg_ctx *c, uint32_t *d_xpar, const uint32_t *d_roots_a, uint32_t off_a, const uint8_t *d_values_a,
+                                      const uint32_t *d_roots_b, uint32_t off_b, const uint8_t *d_values_b, uint32_t n, int threshold, void *stream)
+{
+    if (!c || !d_xpar || (n && (!d_roots_a || !d_roots_b || !d_values_a || !d_values_b))) return fail(RG_ERR_ARG, "bad argument");
+    ON_DEVICE(c->device);
+    if (!n) return RG_OK;
+    const uint32_t thr = threshold <= 0 ? 0u : threshold >= 256 ? 256u : (uint32_t)threshold;
+    k_resolve_union_seam<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(d_xpar, d_roots_a, off_a, d_values_a, d_roots_b, off_b, d_values_b, n, thr);
     CK(cudaGetLastError());
     return RG_OK;
 }
@@ -1452,6 +1502,185 @@ extern "C" int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64
     }
     if (rc == RG_OK) rc = run_all(phase2);
     if (phase_ms) { phase_ms[0] = since(t_start); phase_ms[1] = t1; phase_ms[2] = phase_ms[0] - t1; phase_ms[3] = (float)G; }
+    if (prev_dev >= 0) cudaSetDevice(prev_dev);
+    return rc;
+}
+
+/* ------------------------------------------------------------------ one host IMAGE over a rows x columns grid of GPUs
+ *
+ * The reference spreads its picture over a Cartesian grid of MPI ranks (region.c:537-548 MPI_Dims_create / Cart_create;
+ * distribute_image :106-143; exchange of the four borders :250-353; gather_region :391-432).  rg_grow_multi_grid does
+ * that from one C call: block (i, j) = rows [h*i/R, h*(i+1)/R) x columns [x_j, x_(j+1)) with the column cuts on multiples
+ * of 128 pixels, one block per entry of devices[] (row-major; a device may be named several times).  No halo is exchanged:
+ * a block labels itself with its seams "open" (every pixel of a seam is a cross-tile edge, Params::open), exports for each
+ * seam the local root and the value of every border pixel, and the exchange unites two roots where the two pixels facing
+ * each other across the seam are similar -- the comparison the reference's ranks make on their halo copies.  Every block
+ * resolves the whole seam graph redundantly (as the slabs do) and writes its part of the mask.
+ */
+struct GridBlock {
+    int device; rg_ctx *ctx; cudaStream_t st;
+    uint8_t *img, *mask; size_t img_bytes, mask_bytes;
+    int32_t *seeds; size_t seeds_cap;
+    uint32_t *roots; uint8_t *vals; size_t list_cap;         /* own four border lists: [4][list_cap] */
+    uint32_t *counts_h;                                     /* pinned: {node id space} */
+    uint32_t *all_roots; uint8_t *all_vals; size_t all_cap;  /* every block's lists, gathered */
+    uint32_t *xpar; size_t xpar_words;
+    int64_t x0, x1, y0, y1;
+    int rc; char err[256];
+};
+static GridBlock g_grid[RESOLVE_MAX_RANKS];
+
+extern "C" int rg_grow_multi_grid(const uint8_t *image, int64_t w, int64_t h, const int32_t *seeds_xyz, int nseeds, int threshold,
+                                  uint8_t *mask_out, const int *devices, int rows, int cols, int flags, float *phase_ms)
+{
+    if (!image || !mask_out || w <= 0 || h <= 0 || nseeds < 0 || (nseeds > 0 && !seeds_xyz) || !devices || rows < 1 || cols < 1 || rows * cols > RESOLVE_MAX_RANKS)
+        return fail(RG_ERR_ARG, "bad argument");
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess || have == 0) return fail(RG_ERR_CUDA, "no CUDA device (this library has no CPU path)");
+    for (int g = 0; g < rows * cols; g++) if (devices[g] < 0 || devices[g] >= have) return fail(RG_ERR_ARG, "bad device index");
+    (void)flags;
+    /* cuts: rows anywhere (at least one row per block), columns on multiples of the tile width */
+    const int64_t TXW = Cfg2D::TX;
+    int R = rows, Cn = cols;
+    while (R > 1 && h / R < 1) R--;
+    while (Cn > 1 && (w / Cn) / TXW < 1) Cn--;
+    std::vector<int64_t> xc((size_t)Cn + 1), yc((size_t)R + 1);
+    for (int j = 0; j <= Cn; j++) xc[(size_t)j] = j == Cn ? w : (w * j / Cn) / TXW * TXW;
+    for (int i = 0; i <= R; i++) yc[(size_t)i] = h * i / R;
+    const int B = R * Cn;
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    int prev_dev = -1; cudaGetDevice(&prev_dev);
+    const auto t_start = std::chrono::steady_clock::now();
+    auto since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t).count(); };
+    size_t list_cap = 0;
+    for (int j = 0; j < Cn; j++) list_cap = std::max(list_cap, (size_t)(xc[(size_t)j + 1] - xc[(size_t)j]));
+    for (int i = 0; i < R; i++) list_cap = std::max(list_cap, (size_t)(yc[(size_t)i + 1] - yc[(size_t)i]));
+    auto dev_of = [&](int b) { return devices[(b / Cn) * cols + (b % Cn)]; };       /* the caller's grid is rows x cols; we may use fewer */
+
+    auto phase1 = [&](int b) -> int {
+        GridBlock &m = g_grid[b];
+        m.rc = RG_OK; m.err[0] = 0;
+        const int i = b / Cn, j = b % Cn;
+        m.x0 = xc[(size_t)j]; m.x1 = xc[(size_t)j + 1]; m.y0 = yc[(size_t)i]; m.y1 = yc[(size_t)i + 1];
+        const int64_t bw = m.x1 - m.x0, bh = m.y1 - m.y0;
+        auto bad = [&](int code) { m.rc = code; snprintf(m.err, sizeof m.err, "%s", g_err); return code; };
+#define GCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(RG_ERR_CUDA, #call, e_); return bad(RG_ERR_CUDA); } } while (0)
+        if (m.ctx && m.device != dev_of(b)) {
+            cudaSetDevice(m.device);
+            cudaFree(m.img); cudaFree(m.mask); cudaFree(m.seeds); cudaFree(m.roots); cudaFree(m.vals); cudaFree(m.all_roots); cudaFree(m.all_vals); cudaFree(m.xpar);
+            cudaFreeHost(m.counts_h); cudaStreamDestroy(m.st); rg_ctx_destroy(m.ctx);
+            memset(&m, 0, sizeof m);
+            m.x0 = xc[(size_t)j]; m.x1 = xc[(size_t)j + 1]; m.y0 = yc[(size_t)i]; m.y1 = yc[(size_t)i + 1];
+        }
+        GCK(cudaSetDevice(dev_of(b)));
+        if (!m.ctx) {
+            m.device = dev_of(b);
+            if (rg_ctx_create(m.device, &m.ctx) != RG_OK) return bad(RG_ERR_CUDA);
+            GCK(cudaStreamCreateWithFlags(&m.st, cudaStreamNonBlocking));
+            GCK(cudaHostAlloc((void **)&m.counts_h, 16, cudaHostAllocDefault));
+            for (int o = 0; o < B; o++)
+                if (dev_of(o) != m.device) { int can = 0; cudaDeviceCanAccessPeer(&can, m.device, dev_of(o)); if (can) cudaDeviceEnablePeerAccess(dev_of(o), 0); cudaGetLastError(); }
+        }
+        auto room = [&](void **p, size_t &have_b, size_t want) -> int {
+            if (have_b >= want) return RG_OK;
+            if (*p) { cudaStreamSynchronize(m.st); cudaFree(*p); *p = nullptr; have_b = 0; }
+            GCK(cudaMalloc(p, want)); have_b = want; return RG_OK;
+        };
+        int rc;
+        if ((rc = room((void **)&m.img, m.img_bytes, (size_t)(bw * bh)))) return rc;
+        if ((rc = room((void **)&m.mask, m.mask_bytes, (size_t)(bw * bh)))) return rc;
+        if (m.list_cap < list_cap) {
+            size_t a = m.list_cap * 16, c = m.list_cap * 4;
+            if ((rc = room((void **)&m.roots, a, list_cap * 16))) return rc;
+            if ((rc = room((void **)&m.vals, c, list_cap * 4))) return rc;
+            m.list_cap = list_cap;
+        }
+        /* distribute_image (region.c:106-143): the block's rows out of the picture */
+        GCK(cudaMemcpy2DAsync(m.img, (size_t)bw, image + m.y0 * w + m.x0, (size_t)w, (size_t)bw, (size_t)bh, cudaMemcpyHostToDevice, m.st));
+        std::vector<int32_t> loc;
+        for (int k = 0; k < nseeds; k++) {
+            const int64_t sx = seeds_xyz[3 * k], sy = seeds_xyz[3 * k + 1];
+            if (sx >= m.x0 && sx < m.x1 && sy >= m.y0 && sy < m.y1 && seeds_xyz[3 * k + 2] == 0) { loc.push_back((int32_t)(sx - m.x0)); loc.push_back((int32_t)(sy - m.y0)); loc.push_back(0); }
+        }
+        const int nloc = (int)loc.size() / 3;
+        { size_t sb = m.seeds_cap * 4; if ((rc = room((void **)&m.seeds, sb, (size_t)(nloc > 0 ? 12 * nloc : 12)))) return rc; m.seeds_cap = sb / 4; }
+        if (nloc) { GCK(cudaMemcpyAsync(m.seeds, loc.data(), loc.size() * 4, cudaMemcpyHostToDevice, m.st)); GCK(cudaStreamSynchronize(m.st)); }
+        const int open = (j > 0 ? 1 : 0) | (j < Cn - 1 ? 2 : 0) | (i > 0 ? 4 : 0) | (i < R - 1 ? 8 : 0);
+        if (rg_block_label(m.ctx, m.img, bw, bh, open, nloc ? m.seeds : nullptr, nloc, threshold, m.mask, m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+        for (int side = 0; side < 4; side++)
+            if ((open >> side) & 1)
+                if (rg_block_export(m.ctx, side, m.roots + (size_t)side * m.list_cap, m.vals + (size_t)side * m.list_cap, m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+        GCK(cudaMemcpyAsync(m.counts_h, m.ctx->last_counters + CTR_NODES, 4, cudaMemcpyDeviceToHost, m.st));
+        GCK(cudaStreamSynchronize(m.st));
+        return RG_OK;
+    };
+    std::vector<uint32_t> off((size_t)B + 1, 1u);
+    uint64_t total = 1;
+    auto phase2 = [&](int b) -> int {
+        GridBlock &m = g_grid[b];
+        const int64_t bw = m.x1 - m.x0, bh = m.y1 - m.y0;
+        auto bad = [&](int code) { m.rc = code; snprintf(m.err, sizeof m.err, "%s", g_err); return code; };
+        GCK(cudaSetDevice(m.device));
+        if (B > 1) {
+            auto room = [&](void **p, size_t &have_b, size_t want) -> int {
+                if (have_b >= want) return RG_OK;
+                if (*p) { cudaStreamSynchronize(m.st); cudaFree(*p); *p = nullptr; have_b = 0; }
+                GCK(cudaMalloc(p, want)); have_b = want; return RG_OK;
+            };
+            int rc;
+            if (m.all_cap < (size_t)B * 4 * list_cap) {
+                size_t a = m.all_cap * 4, c = m.all_cap;
+                if ((rc = room((void **)&m.all_roots, a, (size_t)B * 16 * list_cap))) return rc;
+                if ((rc = room((void **)&m.all_vals, c, (size_t)B * 4 * list_cap))) return rc;
+                m.all_cap = (size_t)B * 4 * list_cap;
+            }
+            { size_t xb = m.xpar_words * 4; if ((rc = room((void **)&m.xpar, xb, (size_t)(total + 2) * 4))) return rc; m.xpar_words = xb / 4; }
+            auto len = [&](int o, int side) { const GridBlock &q = g_grid[o]; return (size_t)(side < 2 ? q.y1 - q.y0 : q.x1 - q.x0); };
+            auto has = [&](int o, int side) { const int oi = o / Cn, oj = o % Cn; return side == 0 ? oj > 0 : side == 1 ? oj < Cn - 1 : side == 2 ? oi > 0 : oi < R - 1; };
+            auto R_ = [&](int o, int side) { return m.all_roots + ((size_t)o * 4 + side) * list_cap; };
+            auto V_ = [&](int o, int side) { return m.all_vals + ((size_t)o * 4 + side) * list_cap; };
+            for (int o = 0; o < B; o++)
+                for (int side = 0; side < 4; side++) {
+                    if (!has(o, side)) continue;
+                    GCK(cudaMemcpyPeerAsync(R_(o, side), m.device, g_grid[o].roots + (size_t)side * g_grid[o].list_cap, g_grid[o].device, len(o, side) * 4, m.st));
+                    GCK(cudaMemcpyPeerAsync(V_(o, side), m.device, g_grid[o].vals + (size_t)side * g_grid[o].list_cap, g_grid[o].device, len(o, side), m.st));
+                }
+            GCK(cudaMemsetAsync(m.xpar, 0, 4, m.st));
+            for (int o = 0; o < B; o++)
+                for (int side = 0; side < 4; side++)
+                    if (has(o, side) && rg_slab_resolve_init(m.ctx, m.xpar, R_(o, side), (uint32_t)len(o, side), off[(size_t)o], m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+            for (int o = 0; o < B; o++) {
+                const int oi = o / Cn, oj = o % Cn;
+                if (oj < Cn - 1 && rg_block_resolve_union(m.ctx, m.xpar, R_(o, 1), off[(size_t)o], V_(o, 1), R_(o + 1, 0), off[(size_t)o + 1], V_(o + 1, 0), (uint32_t)len(o, 1), threshold, m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+                if (oi < R - 1 && rg_block_resolve_union(m.ctx, m.xpar, R_(o, 3), off[(size_t)o], V_(o, 3), R_(o + Cn, 2), off[(size_t)o + Cn], V_(o + Cn, 2), (uint32_t)len(o, 3), threshold, m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+            }
+            for (int side = 0; side < 4; side++)
+                if (has(b, side) && rg_slab_resolve_apply(m.ctx, m.xpar, R_(b, side), (uint32_t)len(b, side), off[(size_t)b], m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+        }
+        if (rg_slab_finish(m.ctx, m.st) != RG_OK) return bad(RG_ERR_INTERNAL);
+        /* gather_region (region.c:391-432) */
+        GCK(cudaMemcpy2DAsync(mask_out + m.y0 * w + m.x0, (size_t)w, m.mask, (size_t)bw, (size_t)bw, (size_t)bh, cudaMemcpyDeviceToHost, m.st));
+        GCK(cudaStreamSynchronize(m.st));
+        if (rg_ctx_status(m.ctx, nullptr) != RG_OK) return bad(RG_ERR_INTERNAL);
+        return RG_OK;
+#undef GCK
+    };
+    auto run_all = [&](const std::function<int(int)> &fn) {
+        std::vector<std::thread> th;
+        for (int b = 1; b < B; b++) th.emplace_back([&, b] { fn(b); });
+        fn(0);
+        for (auto &t : th) t.join();
+        for (int b = 0; b < B; b++) if (g_grid[b].rc) { snprintf(g_err, sizeof g_err, "block %d (device %d): %s", b, g_grid[b].device, g_grid[b].err); return g_grid[b].rc; }
+        return (int)RG_OK;
+    };
+    int rc = run_all(phase1);
+    const float t1 = since(t_start);
+    if (rc == RG_OK) {
+        for (int b = 0; b < B; b++) { off[(size_t)b] = (uint32_t)total; total += g_grid[b].counts_h[0]; }
+        if (total + 2 >= (1ull << 32)) rc = fail(RG_ERR_TOO_LARGE, "too many nodes across blocks for 32-bit vertex ids");
+    }
+    if (rc == RG_OK) rc = run_all(phase2);
+    if (phase_ms) { phase_ms[0] = since(t_start); phase_ms[1] = t1; phase_ms[2] = phase_ms[0] - t1; phase_ms[3] = (float)(R * 1000 + Cn); }
     if (prev_dev >= 0) cudaSetDevice(prev_dev);
     return rc;
 }

@@ -166,6 +166,10 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const
     const bool has_zp = C::HZ && ((z0 + C::TZ < nz) || (z0 + vz == nz && ext_zhi<C>(P)));
     const bool has_zm = C::HZ && (z0 > 0 || ext_zlo<C>(P));
     const bool has_xp = x0 + C::TX < nx, has_xm = x0 > 0;
+    /* seams of a block decomposition (Params::open): all valid border pixels, no comparison, no dedupe */
+    const bool live = tmode != 0;
+    const bool open_xm = live && (P.open & 1u) && x0 == 0, open_xp = live && (P.open & 2u) && x0 + C::TX == nx;
+    const bool open_ym = live && (P.open & 4u) && y0 == 0, open_yp = live && (P.open & 8u) && y0 + vy == ny;
     /* y faces: item = (side, z, wx); z faces: item = (side, y, wx) */
     ex.pfor(2 * C::FYW + 2 * C::FZW, [&](int it) {
         const bool zface = it >= 2 * C::FYW;
@@ -175,9 +179,11 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const
         const int wx = r % C::WX, o = r / C::WX;                   /* o = z for y faces, y for z faces */
         int y, z, step, f;
         if (!zface) {
-            if (side ? !has_yp : !has_ym) return;
+            const bool seam = side ? open_yp : open_ym;
+            if (!seam && (side ? !has_yp : !has_ym)) return;
             z = o; y = side ? vy - 1 : 0; step = side ? C::RS : -C::RS; f = side ? F_YP : F_YM;
             if (z >= vz) return;
+            if (seam) { fmask[C::fw_off(f) + o * C::WX + wx] = valid_bits(nx - (x0 + 32 * wx)); return; }
         } else {
             if (side ? !has_zp : !has_zm) return;
             y = o; z = side ? vz - 1 : 0; step = side ? C::PS : -C::PS; f = side ? F_ZP : F_ZM;
@@ -195,10 +201,11 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const
     ex.pfor(2 * C::TY * C::TZ, [&](int it) {
         const int side = it / (C::TY * C::TZ), q = it % (C::TY * C::TZ);
         const int y = q % C::TY, z = q / C::TY;
-        if ((side ? !has_xp : !has_xm) || y >= vy || z >= vz) return;
+        const bool seam = side ? open_xp : open_xm;
+        if ((!seam && (side ? !has_xp : !has_xm)) || y >= vy || z >= vz) return;
         const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
         const uint32_t own = o[0], other = side ? (C::XR ? o[1] : xr[q]) : o[-1];       /* lean layout: the x = TX column is in xr */
-        if (absdiff(own, other) < P.thr) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
+        if (seam || absdiff(own, other) < P.thr) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
     });
 }
 

@@ -79,7 +79,41 @@ RG_FN void export_interface(Exec &ex, const Params &P, int side, uint32_t *out_r
 }
 #endif
 
+/* ---- blocks of an image (rows x columns): the four borders of a block labelled with Params::open ----
+   side 0 / 1 / 2 / 3 = -x / +x / -y / +y.  One entry per border pixel, in pixel order: the local root of its component and
+   the pixel's value (the exchange compares the values across the seam: no halo was read when the block was labelled). */
+template <class C> RG_HDFN int64_t border_len(const Params &P, int side) { return side < 2 ? P.ny : P.nx; }
+template <class C, class Exec>
+RG_FN void export_border(Exec &ex, const Params &P, int side, uint32_t *out_roots, uint8_t *out_vals)
+{
+    const int f = side;                                           /* F_XM, F_XP, F_YM, F_YP */
+    ex.gpfor(border_len<C>(P, side), [&](int64_t i) {
+        const int64_t x = side == 0 ? 0 : side == 1 ? P.nx - 1 : i, y = side == 2 ? 0 : side == 3 ? P.ny - 1 : i;
+        const uint32_t tile = (uint32_t)(y / C::TY) * (uint32_t)P.ntx + (uint32_t)(x / C::TX);
+        const TileRec &rc = P.rec[tile];
+        uint32_t off = 0;
+        for (int k = 0; k < f; k++) off += rc.cnt[k];
+        const uint32_t idx = (uint32_t)(side < 2 ? y % C::TY : x % C::TX);      /* every valid border pixel is an entry, in order */
+        uint32_t r = 1u;                                            /* (a valid vertex, should the self-check below ever fire) */
+        if (P.tmode == 0) r = 0u;                                   /* threshold <= 0: no pixel is similar to any other, nothing to exchange */
+        else if (idx < rc.cnt[f]) r = find32(P.nparent, rc.node_base + P.ent[(size_t)tile * C::ENT_MAX + off + idx]);
+        else atomic_or(&P.counters[CTR_STATUS], ST_FACE_MISMATCH);
+        out_roots[i] = r;
+        out_vals[i] = P.image[y * P.nx + x];
+    });
+}
+
 RG_FN uint32_t xvertex(uint32_t root, uint32_t off) { return root ? off + root : 0u; }
+
+/* a seam between two blocks: entry i of both lists faces entry i of the other; united where the two pixels are similar */
+template <class Exec>
+RG_FN void resolve_union_seam(Exec &ex, uint32_t *xpar, const uint32_t *a, uint32_t offa, const uint8_t *va,
+                              const uint32_t *b, uint32_t offb, const uint8_t *vb, uint32_t n, uint32_t thr)
+{
+    ex.gpfor((int64_t)n, [&](int64_t i) {
+        if (absdiff(va[i], vb[i]) < thr) unite32(xpar, xvertex(a[i], offa), xvertex(b[i], offb));
+    });
+}
 
 /* lazily initialise only the vertices that appear on an interface */
 template <class Exec>

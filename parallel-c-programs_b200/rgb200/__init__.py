@@ -33,6 +33,10 @@ SIGNATURES = {
     "rg_grow": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_grow_sparse": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_host_stats": (_i32, [_vp]),
+    "rg_grow_multi_grid": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _vp]),
+    "rg_block_label": (_i32, [_vp, _vp, _i64, _i64, _i32, _vp, _i32, _i32, _vp, _vp]),
+    "rg_block_export": (_i32, [_vp, _i32, _vp, _vp, _vp]),
+    "rg_block_resolve_union": (_i32, [_vp, _vp, _vp, _u32, _vp, _vp, _u32, _vp, _u32, _i32, _vp]),
     "rg_grow_multi": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _vp]),
     "rg_ctx_create": (_i32, [_i32, _c.POINTER(_vp)]),
     "rg_ctx_destroy": (None, [_vp]),

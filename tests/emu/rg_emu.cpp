@@ -245,6 +245,74 @@ extern "C" int emu_grow_slabs(int cfg, int G, const uint8_t *image, int64_t nx, 
     return emu_grow_slabs_t<CfgT3>(G, image, nx, ny, nz, seeds, nseeds, T, mask, stats);
 }
 
+/* ---- an image over a rows x columns grid of blocks: the protocol of rg_grow_multi_grid on host memory ---- */
+template <class C>
+static int emu_grow_grid_t(int R, int Cn, const uint8_t *image, int64_t w, int64_t h, const int32_t *seeds, int nseeds, int T, uint8_t *mask, uint32_t *stats)
+{
+    while (R > 1 && h / R < 1) R--;
+    while (Cn > 1 && (w / Cn) / C::TX < 1) Cn--;
+    std::vector<int64_t> xc((size_t)Cn + 1), yc((size_t)R + 1);
+    for (int j = 0; j <= Cn; j++) xc[(size_t)j] = j == Cn ? w : (w * j / Cn) / C::TX * C::TX;
+    for (int i = 0; i <= R; i++) yc[(size_t)i] = h * i / R;
+    const int B = R * Cn;
+    std::vector<EmuState> E((size_t)B);
+    std::vector<std::vector<uint8_t>> img((size_t)B), msk((size_t)B);
+    std::vector<std::vector<int32_t>> sl((size_t)B);
+    std::vector<std::vector<uint32_t>> roots((size_t)B * 4);
+    std::vector<std::vector<uint8_t>> vals((size_t)B * 4);
+    HostExec ex;
+    const uint32_t thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
+    for (int b = 0; b < B; b++) {
+        const int i = b / Cn, j = b % Cn;
+        const int64_t x0 = xc[(size_t)j], x1 = xc[(size_t)j + 1], y0 = yc[(size_t)i], y1 = yc[(size_t)i + 1], bw = x1 - x0, bh = y1 - y0;
+        img[(size_t)b].resize((size_t)(bw * bh) + 64); msk[(size_t)b].assign((size_t)(bw * bh), 7);
+        uint8_t *base = (uint8_t *)(((uintptr_t)img[(size_t)b].data() + 15) & ~(uintptr_t)15);
+        for (int64_t y = 0; y < bh; y++) memcpy(base + y * bw, image + (y0 + y) * w + x0, (size_t)bw);
+        for (int k = 0; k < nseeds; k++) {
+            const int64_t sx = seeds[3 * k], sy = seeds[3 * k + 1];
+            if (sx >= x0 && sx < x1 && sy >= y0 && sy < y1 && seeds[3 * k + 2] == 0) { sl[(size_t)b].push_back((int32_t)(sx - x0)); sl[(size_t)b].push_back((int32_t)(sy - y0)); sl[(size_t)b].push_back(0); }
+        }
+        emu_setup<C>(E[(size_t)b], base, bw, bh, 1, 0, 0, sl[(size_t)b].data(), (int)sl[(size_t)b].size() / 3, T, msk[(size_t)b].data());
+        E[(size_t)b].P.open = (j > 0 ? 1u : 0u) | (j < Cn - 1 ? 2u : 0u) | (i > 0 ? 4u : 0u) | (i < R - 1 ? 8u : 0u);
+        emu_label<C>(E[(size_t)b]);
+        for (int side = 0; side < 4; side++)
+            if ((E[(size_t)b].P.open >> side) & 1u) {
+                const size_t n = (size_t)(side < 2 ? bh : bw);
+                roots[(size_t)b * 4 + side].assign(n, 0); vals[(size_t)b * 4 + side].assign(n, 0);
+                export_border<C>(ex, E[(size_t)b].P, side, roots[(size_t)b * 4 + side].data(), vals[(size_t)b * 4 + side].data());
+            }
+    }
+    std::vector<uint32_t> off((size_t)B + 1, 1u);
+    for (int b = 0; b < B; b++) off[(size_t)b + 1] = off[(size_t)b] + E[(size_t)b].counters[CTR_NODES];
+    std::vector<uint32_t> xpar(off[(size_t)B] + 2, 0);
+    for (int b = 0; b < B; b++)
+        for (int side = 0; side < 4; side++) { auto &r = roots[(size_t)b * 4 + side]; if (!r.empty()) resolve_init(ex, xpar.data(), r.data(), (uint32_t)r.size(), off[(size_t)b]); }
+    xpar[0] = 0;
+    for (int b = 0; b < B; b++) {
+        const int i = b / Cn, j = b % Cn;
+        if (j < Cn - 1) { auto &a = roots[(size_t)b * 4 + 1]; auto &c2 = roots[(size_t)(b + 1) * 4 + 0];
+            resolve_union_seam(ex, xpar.data(), a.data(), off[(size_t)b], vals[(size_t)b * 4 + 1].data(), c2.data(), off[(size_t)b + 1], vals[(size_t)(b + 1) * 4].data(), (uint32_t)a.size(), thr); }
+        if (i < R - 1) { auto &a = roots[(size_t)b * 4 + 3]; auto &c2 = roots[(size_t)(b + Cn) * 4 + 2];
+            resolve_union_seam(ex, xpar.data(), a.data(), off[(size_t)b], vals[(size_t)b * 4 + 3].data(), c2.data(), off[(size_t)b + Cn], vals[(size_t)(b + Cn) * 4 + 2].data(), (uint32_t)a.size(), thr); }
+    }
+    uint32_t st = 0;
+    for (int b = 0; b < B; b++) {
+        for (int side = 0; side < 4; side++) { auto &r = roots[(size_t)b * 4 + side]; if (!r.empty()) resolve_apply(ex, E[(size_t)b].P, xpar.data(), r.data(), (uint32_t)r.size(), off[(size_t)b]); }
+        emu_finish<C>(E[(size_t)b]);
+        st |= E[(size_t)b].counters[CTR_STATUS];
+        const int i = b / Cn, j = b % Cn;
+        const int64_t x0 = xc[(size_t)j], bw = xc[(size_t)j + 1] - x0, y0 = yc[(size_t)i], bh = yc[(size_t)i + 1] - y0;
+        for (int64_t y = 0; y < bh; y++) memcpy(mask + (y0 + y) * w + x0, msk[(size_t)b].data() + y * bw, (size_t)bw);
+    }
+    if (stats) { stats[0] = off[(size_t)B]; stats[1] = st; stats[2] = (uint32_t)R; stats[3] = (uint32_t)Cn; }
+    return st ? -4 : 0;
+}
+extern "C" int emu_grow_grid(int cfg, int R, int Cn, const uint8_t *image, int64_t w, int64_t h, const int32_t *seeds, int nseeds, int T, uint8_t *mask, uint32_t *stats)
+{
+    return cfg == 0 ? emu_grow_grid_t<Cfg2D>(R, Cn, image, w, h, seeds, nseeds, T, mask, stats)
+                    : emu_grow_grid_t<CfgS2>(R, Cn, image, w, h, seeds, nseeds, T, mask, stats);
+}
+
 /* ---- the slab phases of include/rg.h on HOST memory, same names and signatures, so that the
  * `not gpu` tests can drive rgb200.SlabGrower over the gloo backend with CPU tensors.  TEST ONLY. ---- */
 static int g_cfg = 1;

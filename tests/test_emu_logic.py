@@ -337,3 +337,31 @@ def test_emu_row_tiles(emu, oracle, cfg):
     img3, s3, T3 = oracle.synth("c3", 192 if cfg != 1 else 96)
     got, _ = run_emu(emu, cfg, img3, s3, T3)
     assert (got == oracle.grow(img3, s3, T3)).all() and emu.emu_last_rows() > 0
+
+
+@pytest.mark.parametrize("R,Cn", [(1, 2), (2, 1), (2, 2), (3, 4), (4, 3)])
+@pytest.mark.parametrize("cfg,shape", [(1, (40, 160)), (1, (33, 131)), (0, (260, 530)), (1, (9, 64))])
+def test_emu_image_over_a_grid_of_blocks(emu, oracle, golden, R, Cn, cfg, shape):
+    """an image cut into rows x columns blocks (the reference's Cartesian process grid, region.c:537-548, 106-143): every block
+    labels itself with open seams, the exchange compares the pixel pairs across each seam; ragged blocks, seeds on seams,
+    snakes that cross seams many times"""
+    emu.emu_grow_grid.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, u8p, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                  ctypes.c_int, u8p, ctypes.c_void_p]
+    rng = np.random.default_rng(abs(hash((R, Cn, cfg, shape))) % 2**32)
+    h, w = shape
+    for levels, T in ((3, 1), (6, 2), (2, 1), (5, 300), (4, 0)):
+        img = rng.integers(0, levels, size=shape, dtype=np.uint8)
+        img[h // 3, :] = 1                                             # a line through every column of blocks
+        img[:, w // 2 - 1: w // 2 + 1] = 1                             # ... and through every row of blocks
+        seeds = np.stack([rng.integers(0, w, 6), rng.integers(0, h, 6), np.zeros(6, np.int64)], 1).astype(np.int32)
+        seeds[0] = [w // 2, h // 3, 0]
+        want = oracle.grow(img, seeds, T)
+        got = np.full(shape, 9, np.uint8); st = np.zeros(4, np.uint32)
+        rc = emu.emu_grow_grid(cfg, R, Cn, img.ctypes.data, w, h, seeds.ctypes.data, len(seeds), T, got.ctypes.data, st.ctypes.data)
+        assert rc == 0 and (got == want).all(), (levels, T, list(st))
+    if cfg == 0 and R * Cn >= 4:
+        pic = golden["arrays"]["pic1"]
+        s = oracle.seeds_2d(512, 512)
+        got = np.empty_like(pic); st = np.zeros(4, np.uint32)
+        assert emu.emu_grow_grid(0, R, Cn, pic.ctypes.data, 512, 512, s.ctypes.data, 4, 2, got.ctypes.data, st.ctypes.data) == 0
+        assert (got == oracle.grow(pic, s, 2)).all() and int(st[2]) == R and int(st[3]) == min(Cn, 4)

@@ -584,3 +584,39 @@ def test_row_tiles_on_gpu(rg, ctx, oracle, monkeypatch):
     want3 = oracle.grow(img3, s3, T3)
     got3 = dev_grow(rg, ctx, img3, s3, T3)
     assert (got3 == want3).all()
+
+
+@pytest.mark.parametrize("R,Cn", [(1, 2), (2, 2), (3, 4), (2, 1)])
+def test_grow_multi_grid_from_c_abi(rg, oracle, golden, R, Cn):
+    """rg_grow_multi_grid: one host image over a rows x columns grid of blocks (the reference's Cartesian process grid,
+    region.c:537-548; blocks dealt round-robin to the GPUs this box has), open seams, one exchange that compares the pixel
+    pairs across every seam, the mask gathered block by block -- against the oracle on the four reference pictures' kind of
+    input, a noise image with lines through every seam, and C2's geometry"""
+    import torch
+    lib = rg.load_library()
+    ndev = torch.cuda.device_count()
+    devices = (ctypes.c_int * (R * Cn))(*[b % ndev for b in range(R * Cn)])
+
+    def run(img, seeds, T):
+        img = np.ascontiguousarray(img, np.uint8); h, w = img.shape
+        seeds = np.ascontiguousarray(np.asarray(seeds, np.int32).reshape(-1, 3))
+        out = np.full(img.shape, 9, np.uint8); ms = (ctypes.c_float * 4)()
+        rc = lib.rg_grow_multi_grid(img.ctypes.data, w, h, seeds.ctypes.data if len(seeds) else None, len(seeds), T, out.ctypes.data,
+                                    devices, R, Cn, 0, ms)
+        assert rc == 0, lib.rg_last_error()
+        return out, int(ms[3])
+
+    pic = golden["arrays"]["pic1"]; s = oracle.seeds_2d(512, 512)
+    got, used = run(pic, s, 2)
+    assert (got == oracle.grow(pic, s, 2)).all() and used == 1000 * R + min(Cn, 4)
+    rng = np.random.default_rng(60 + R * 10 + Cn)
+    img = rng.integers(0, 4, size=(700, 1111), dtype=np.uint8); img[233, :] = 1; img[:, 554:556] = 1; img[300:500, 100:900] = 77
+    seeds = np.stack([rng.integers(0, 1111, 8), rng.integers(0, 700, 8), np.zeros(8, np.int64)], 1).astype(np.int32); seeds[0] = [555, 233, 0]
+    for T in (1, 2, 256):
+        got, _ = run(img, seeds, T)
+        assert (got == oracle.grow(img, seeds, T)).all(), T
+    img2, s2, T2 = oracle.synth("c2", 2048, 0x5EED0002)
+    got, _ = run(img2, s2, T2)
+    assert (got == oracle.grow(img2, s2, T2)).all()
+    got, _ = run(img2, np.zeros((0, 3), np.int32), T2)
+    assert not got.any()
