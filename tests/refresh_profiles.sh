@@ -1,0 +1,34 @@
+#!/bin/bash
+# tests/refresh_profiles.sh -- turn the reports of tests/profile_r02.sh (gpurun_out/) into the committed profiles/r02_* files
+cd "$(dirname "$0")/.." || exit 1
+H=$(git rev-parse --short HEAD)
+S="python3 tests/summarise_ncu.py"
+{ echo "# Round 2 -- ncu evidence, k_pass_a_fast on C4 2048^3 (bench default)"; echo
+  echo "Command (exited 0 without ncu first, same gpurun call, tests/profile_r02.sh): \`python bench.py --no-extras --steps 2 --warmup 1\`, then"
+  echo "\`ncu --set full --clock-control none --import-source on -k regex:k_pass_a_fast --launch-skip 1 --launch-count 1\`. Build: commit $H."
+  echo "Algorithmic bytes of this kernel per launch: 2 B x 2048^3 = 17.18 GB (reads every voxel once, clears every mask byte once)."; echo
+  $S gpurun_out/r02_fast_c4.ncu-rep; } > profiles/r02_ncu_pass_a_fast_C4.md
+{ echo "# Round 2 -- ncu evidence, merge / flag / pass C on C4 2048^3"; echo
+  echo "Same command as r02_ncu_pass_a_fast_C4.md, \`-k regex:\"k_merge|k_pass_c|k_flag_tiles\" --launch-skip 3 --launch-count 3\`. Build: commit $H."; echo
+  cat profiles/notes_r02_rest_c4.txt 2>/dev/null; echo
+  $S gpurun_out/r02_rest_c4.ncu-rep; } > profiles/r02_ncu_merge_flag_passc_C4.md
+for wl in C3 C1 C2; do
+  { echo "# Round 2 -- ncu evidence, the kernels of one grow on $wl"; echo
+    echo "Command (exited 0 without ncu first): \`python bench.py --no-extras --steps 2 --warmup 1 --workload $wl\`, then \`ncu --set full --clock-control none --import-source on -k regex:\"k_pass_a_fast|k_merge|k_pass_c|k_flag_tiles\" --launch-skip 4 --launch-count 4\`. Build: commit $H."
+    cat profiles/notes_r02_$wl.txt 2>/dev/null; echo
+    $S gpurun_out/r02_all_$wl.ncu-rep; } > profiles/r02_ncu_$wl.md
+done
+cp gpurun_out/r02_launches_C4_2048.csv profiles/r02_launches_C4_2048.csv
+python3 - <<PY
+import csv, json, subprocess, io
+out = subprocess.run(["ncu", "-i", "gpurun_out/r02_fast_c4.ncu-rep", "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(out))); h, u, r = rows[0], rows[1], rows[2]
+def g(m):
+    v = float(r[h.index(m)]); unit = u[h.index(m)]
+    return v * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1, "ms": 1, "us": 1e-3, "s": 1e3}.get(unit, 1)
+rd, wr, ms = g("dram__bytes_read.sum"), g("dram__bytes_write.sum"), g("gpu__time_duration.sum")
+json.dump({"kernel": "k_pass_a_fast", "workload": "C4 2048^3, 16 seeds (bench default)", "dram_bytes_read": rd, "dram_bytes_write": wr,
+           "dram_bytes_total": rd + wr, "kernel_ms": ms, "algorithmic_bytes": 2 * 2048 ** 3, "captured_at_commit": "$H",
+           "source": "profiles/r02_ncu_pass_a_fast_C4.md (ncu --set full --clock-control none, one launch)"}, open("profiles/traffic_r02.json", "w"), indent=1)
+print(open("profiles/traffic_r02.json").read())
+PY
