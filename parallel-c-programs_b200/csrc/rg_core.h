@@ -66,10 +66,9 @@ struct TileCfg {
     static_assert(TX % 32 == 0, "rows are whole words");
     static_assert(NV <= 65536, "16-bit tile-local indices");
     static_assert(NW % 4 == 0, "bit sets are cleared 16 bytes at a time");
-    RG_MFN static constexpr int fw_off(int f)
+    RG_MFN static constexpr int fw_off(int f)               /* first mask word of face f: branch-free, f is often a run-time value */
     {
-        return f == 0 ? 0 : f == 1 ? FXW : f == 2 ? 2 * FXW : f == 3 ? 2 * FXW + FYW
-             : f == 4 ? 2 * FXW + 2 * FYW : f == 5 ? 2 * FXW + 2 * FYW + FZW : FW_TOTAL;
+        return (f > 0) * FXW + (f > 1) * FXW + (f > 2) * FYW + (f > 3) * FYW + (f > 4) * FZW + (f > 5) * FZW;
     }
 };
 

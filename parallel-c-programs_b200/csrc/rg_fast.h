@@ -332,7 +332,7 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         ex.pfor(C::FW_TOTAL, [&](int fw) {
             uint32_t m = s.v.e.u.f.fmask[fw];
             if (!m) return;
-            int f = 0; while (fw >= C::fw_off(f + 1)) f++;
+            const int f = (fw >= C::fw_off(1)) + (fw >= C::fw_off(2)) + (fw >= C::fw_off(3)) + (fw >= C::fw_off(4)) + (fw >= C::fw_off(5));
             const int idx = fw - C::fw_off(f);
             uint32_t slot = s.v.e.u.f.fprefix[fw];
             while (m) { int b = ffs1(m) - 1; m &= m - 1; s.ent_root[slot++] = (uint16_t)face_voxel<C>(f, idx, b, vy, vz); }
