@@ -412,12 +412,12 @@ def main():
             img = torch.empty((n, n), dtype=torch.uint8, device=dev); ctx.synth(kind, img, n, seed)
             out = torch.empty_like(img); d_seeds = torch.from_numpy(seeds_np).to(dev)
             step = lambda: ctx.grow(img, d_seeds, T, out)
-            nvox, launches = n * n, 7          # keys, sort, fast label, full label, merge, flag/zero, pass C
+            nvox, launches = n * n, 7          # keys, sort, labelling pass, full pass (overflow list), merge, flag, pass C
         elif world == 1:
             img = torch.empty((n, n, n), dtype=torch.uint8, device=dev); ctx.synth(kind, img, n, seed)
             out = torch.empty_like(img); d_seeds = torch.from_numpy(seeds_np).to(dev)
             step = lambda: ctx.grow(img, d_seeds, T, out)
-            nvox, launches = n ** 3, 6 + (1 if len(seeds_np) > 1 else 0)
+            nvox, launches = n ** 3, 7 + (1 if len(seeds_np) > 1 else 0)     # keys, [sort], labelling, full (overflow list), merge, flag, row-tile output, pass C
         else:
             g = rgb200.SlabGrower(lib, ctx.handle, n, n, n, rank, world, dev)
             plane = n * n
@@ -428,7 +428,7 @@ def main():
             step = lambda: g.grow(T)
             img, out = g.image, g.mask
             nvox = n ** 3
-            launches = 6 + 4 + (2 * world + (world - 1) + 2) + 2   # label, 2x export (2 kernels each), resolve init/union/apply, flag + pass C (upper bound)
+            launches = 6 + 4 + 4 + 3                            # label (keys, sort, labelling, full, merge), export (memset + 2 x 2 kernels), resolve (prepare, init, union, apply), flag + row output + pass C
         for _ in range(warmup):
             step()
         barrier()
