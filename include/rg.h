@@ -240,6 +240,21 @@ int rg_slab_resolve_packed(rg_ctx *ctx, uint32_t *d_xpar, uint32_t xpar_cap, con
 /* pass C on the slab labelled last */
 int rg_slab_finish(rg_ctx *ctx, void *stream);
 
+/* The packed exchange without a gather: rank r exports into a buffer the other processes of the node have mapped (rg_ipc_alloc /
+ * rg_ipc_open below), the ranks meet at one small barrier (any all-reduce on the stream), and rg_slab_resolve_peers reads every
+ * rank's record where it lies -- d_peer_records is a DEVICE array of `world` pointers, entry r = rank r's record in this process's
+ * address space (its own buffer for r == rank).  The lists cross NVLink inside the resolve kernels (plain peer loads).  Alternate
+ * two export buffers from step to step: a fast rank may export its next step while a slow one still reads this one.
+ * No counterpart in the reference (its exchange() is four MPI_Send / MPI_Recv pairs per round, region.c:250-353). */
+int rg_slab_resolve_peers(rg_ctx *ctx, uint32_t *d_xpar, uint32_t xpar_cap, const uint32_t *const *d_peer_records, uint32_t cap,
+                          int rank, int world, void *stream);
+/* device buffers that other processes on the node can map: rg_ipc_alloc = cudaMalloc + the 64-byte handle to hand to the peers
+ * (torch.distributed, MPI, a pipe ...), rg_ipc_open maps a peer's buffer, rg_ipc_close unmaps it, rg_ipc_free frees one's own. */
+int rg_ipc_alloc(int64_t bytes, void **d_ptr_out, unsigned char handle_out[64]);
+int rg_ipc_open(const unsigned char handle[64], void **d_ptr_out);
+int rg_ipc_close(void *d_ptr);
+int rg_ipc_free(void *d_ptr);
+
 /* ---- synthetic inputs on the device (replaces func()/create_data(), raycast.cu:114-158) ---- */
 /* kind: 1 = exercise geometry with hash noise (C1h), 2 = C2 image (n x n), 3 = C3 serpentine,
  * 4 = C4 (exercise geometry + z-serpentine).  Cube / square of side n; seed = noise seed. */

@@ -343,9 +343,9 @@ __global__ void __launch_bounds__(256) k_resolve_union_seam(uint32_t *xpar, cons
     resolve_union_seam(ex, xpar, a, offa, va, b, offb, vb, n, thr);
 }
 __global__ void k_resolve_prepare(const Params P, const uint32_t *packed_all, uint32_t stride_words, uint32_t cap, uint32_t xpar_cap,
-                                  uint32_t rank, uint32_t world, ResolveArgs *A, uint32_t *xpar)
+                                  uint32_t rank, uint32_t world, ResolveArgs *A, uint32_t *xpar, const uint32_t *const *peer_records)
 {
-    if (blockIdx.x == 0 && threadIdx.x == 0) { xpar[0] = 0; resolve_prepare(P, packed_all, stride_words, cap, xpar_cap, rank, world, A); }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { xpar[0] = 0; resolve_prepare(P, packed_all, stride_words, cap, xpar_cap, rank, world, A, peer_records); }
 }
 __global__ void __launch_bounds__(256) k_resolve_init_packed(uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs *A)
 {
@@ -896,7 +896,7 @@ extern "C" int rg_slab_resolve_packed(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar
     ON_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
     const uint32_t stride = 4u + 2u * cap;
-    k_resolve_prepare<<<1, 32, 0, st>>>(c->last_P, d_packed_all, stride, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, c->d_rargs, d_xpar);
+    k_resolve_prepare<<<1, 32, 0, st>>>(c->last_P, d_packed_all, stride, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, c->d_rargs, d_xpar, nullptr);
     k_resolve_init_packed<<<blocks_for((uint32_t)world * 2u * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
     k_resolve_union_packed<<<blocks_for((uint32_t)(world - 1) * cap), 256, 0, st>>>(d_xpar, d_packed_all, cap, c->d_rargs);
     k_resolve_apply_packed<<<blocks_for(2u * cap), 256, 0, st>>>(c->last_P, d_xpar, d_packed_all, cap, c->d_rargs);
@@ -938,6 +938,47 @@ extern "C" int rg_block_resolve_union(rg_ctx *c, uint32_t *d_xpar, const uint32_
     CK(cudaGetLastError());
     return RG_OK;
 }
+
+/* the same resolve, reading every rank's packed record where that rank exported it (d_peer_records: device array of `world`
+   pointers, entry r = rank r's export buffer as mapped into this process): no gather step, the lists cross NVLink inside the
+   resolve kernels */
+extern "C" int rg_slab_resolve_peers(rg_ctx *c, uint32_t *d_xpar, uint32_t xpar_cap, const uint32_t *const *d_peer_records, uint32_t cap,
+                                     int rank, int world, void *stream)
+{
+    if (!c || !c->have_last || !d_xpar || !d_peer_records || !cap || world < 2 || world > RESOLVE_MAX_RANKS || rank < 0 || rank >= world)
+        return fail(RG_ERR_ARG, "bad argument");
+    ON_DEVICE(c->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    k_resolve_prepare<<<1, 32, 0, st>>>(c->last_P, nullptr, 4u + 2u * cap, cap, xpar_cap, (uint32_t)rank, (uint32_t)world, c->d_rargs, d_xpar, d_peer_records);
+    k_resolve_init_packed<<<blocks_for((uint32_t)world * 2u * cap), 256, 0, st>>>(d_xpar, nullptr, cap, c->d_rargs);
+    k_resolve_union_packed<<<blocks_for((uint32_t)(world - 1) * cap), 256, 0, st>>>(d_xpar, nullptr, cap, c->d_rargs);
+    k_resolve_apply_packed<<<blocks_for(2u * cap), 256, 0, st>>>(c->last_P, d_xpar, nullptr, cap, c->d_rargs);
+    CK(cudaGetLastError());
+    return RG_OK;
+}
+
+/* Buffers other processes on this node can map: plain cudaMalloc blocks (an allocation base, which is what an IPC handle names)
+   and the 64-byte handles to pass around (any transport: torch.distributed, MPI, a pipe). */
+extern "C" int rg_ipc_alloc(int64_t bytes, void **d_ptr_out, unsigned char handle_out[64])
+{
+    if (bytes <= 0 || !d_ptr_out || !handle_out) return fail(RG_ERR_ARG, "bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handles are 64 bytes");
+    CK(cudaMalloc(d_ptr_out, (size_t)bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr_out);
+    if (e != cudaSuccess) { cudaFree(*d_ptr_out); *d_ptr_out = nullptr; return fail(RG_ERR_CUDA, "cudaIpcGetMemHandle", e); }
+    memcpy(handle_out, &h, 64);
+    return RG_OK;
+}
+extern "C" int rg_ipc_open(const unsigned char handle[64], void **d_ptr_out)
+{
+    if (!handle || !d_ptr_out) return fail(RG_ERR_ARG, "bad argument");
+    cudaIpcMemHandle_t h; memcpy(&h, handle, 64);
+    CK(cudaIpcOpenMemHandle(d_ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return RG_OK;
+}
+extern "C" int rg_ipc_close(void *d_ptr) { if (d_ptr) CK(cudaIpcCloseMemHandle(d_ptr)); return RG_OK; }
+extern "C" int rg_ipc_free(void *d_ptr) { if (d_ptr) CK(cudaFree(d_ptr)); return RG_OK; }
 
 extern "C" int rg_slab_finish(rg_ctx *c, void *stream)
 {

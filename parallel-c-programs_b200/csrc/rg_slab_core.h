@@ -145,6 +145,8 @@ struct ResolveArgs {
     uint32_t world, rank, stride, pad;
     uint32_t cnt[RESOLVE_MAX_RANKS][2];
     uint32_t off[RESOLVE_MAX_RANKS];
+    const uint32_t *base[RESOLVE_MAX_RANKS];   /* packed exchange: where rank r's record lives -- a slice of the gathered buffer, or that
+                                                  rank's own export buffer mapped into this process (peer reads over NVLink, no gather) */
 };
 
 template <class Exec>
@@ -182,13 +184,14 @@ RG_FN void resolve_apply_all(Exec &ex, const Params &P, uint32_t *xpar, const ui
    work) if a list outgrew `cap` or the vertex space outgrew `xpar_cap`. */
 enum { ST_EXCHANGE_OVERFLOW = 4u };
 RG_FN void resolve_prepare(const Params &P, const uint32_t *packed_all, uint32_t stride_words, uint32_t cap, uint32_t xpar_cap,
-                           uint32_t rank, uint32_t world, ResolveArgs *A)
+                           uint32_t rank, uint32_t world, ResolveArgs *A, const uint32_t *const *peer_records = nullptr)
 {
     bool ok = true;
     uint64_t off = 1;
     A->world = world; A->rank = rank; A->stride = stride_words; A->pad = 0;
     for (uint32_t r = 0; r < world; r++) {
-        const uint32_t *h = packed_all + (size_t)r * stride_words;
+        const uint32_t *h = peer_records ? peer_records[r] : packed_all + (size_t)r * stride_words;
+        A->base[r] = h;
         A->cnt[r][0] = h[0]; A->cnt[r][1] = h[1];
         if (h[0] > cap || h[1] > cap) ok = false;
         A->off[r] = (uint32_t)off; off += h[2];
@@ -201,9 +204,9 @@ RG_FN void resolve_prepare(const Params &P, const uint32_t *packed_all, uint32_t
     }
 }
 /* list of (rank r, side) inside the packed buffer: header of 4 words, then the two lists */
-RG_FN const uint32_t *packed_list(const uint32_t *packed_all, const ResolveArgs &A, uint32_t cap, uint32_t r, uint32_t side)
+RG_FN const uint32_t *packed_list(const uint32_t *, const ResolveArgs &A, uint32_t cap, uint32_t r, uint32_t side)
 {
-    return packed_all + (size_t)r * A.stride + 4 + (size_t)side * cap;
+    return A.base[r] + 4 + (size_t)side * cap;
 }
 template <class Exec>
 RG_FN void resolve_init_packed(Exec &ex, uint32_t *xpar, const uint32_t *packed_all, uint32_t cap, const ResolveArgs &A)

@@ -62,6 +62,11 @@ SIGNATURES = {
     "rg_slab_export_packed": (_i32, [_vp, _vp, _u32, _vp]),
     "rg_slab_resolve_packed": (_i32, [_vp, _vp, _u32, _vp, _u32, _i32, _i32, _vp]),
     "rg_slab_finish": (_i32, [_vp, _vp]),
+    "rg_slab_resolve_peers": (_i32, [_vp, _vp, _u32, _vp, _u32, _i32, _i32, _vp]),
+    "rg_ipc_alloc": (_i32, [_i64, _c.POINTER(_vp), _vp]),
+    "rg_ipc_open": (_i32, [_vp, _c.POINTER(_vp)]),
+    "rg_ipc_close": (_i32, [_vp]),
+    "rg_ipc_free": (_i32, [_vp]),
     "rg_synth_device": (_i32, [_i32, _vp, _i64, _u64, _vp]),
     "rg_synth_slab_device": (_i32, [_i32, _vp, _i64, _i64, _i64, _u64, _vp]),
     "rg_synth_seeds": (_i32, [_i32, _i64, _u64, _vp, _i32]),

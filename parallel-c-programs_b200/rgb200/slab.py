@@ -57,6 +57,7 @@ class SlabGrower:
         self.rounds = 0
         self._timing = None
         self._cap = None            # capacities learnt from the last synchronous exchange (optimistic mode)
+        self._peers, self._peer_handles, self._peer_turn = None, [], 0     # export buffers mapped by the peers (CUDA IPC), see _map_peer_buffers
         self._xpar_cap = 0
         self.optimistic_steps = 0
 
@@ -103,6 +104,64 @@ class SlabGrower:
         for w in dist.batch_isend_irecv(ops):
             w.wait()
 
+    def _release_peer_buffers(self):
+        for own, table, opened in getattr(self, "_peer_handles", []):
+            for p in opened:
+                self.lib.rg_ipc_close(ctypes.c_void_p(p))
+            self.lib.rg_ipc_free(ctypes.c_void_p(own))
+        self._peer_handles, self._peers = [], None
+
+    def _map_peer_buffers(self):
+        """(collective) two export buffers per rank that the other ranks of the node map through CUDA IPC, and for each a device
+        table of every rank's buffer address in THIS process.  Falls back to the all-gather exchange where the library or the
+        platform has no IPC (the CPU emulator of the tests, RG_NO_PEER_EXCHANGE=1)."""
+        import os
+        torch, dist, lib = self.torch, self.dist, self.lib
+        self._release_peer_buffers()
+        self._peer_turn = 0
+        ok = hasattr(lib, "rg_ipc_alloc") and self.use_cuda_stream and not os.environ.get("RG_NO_PEER_EXCHANGE")
+        nbytes = 4 * (4 + 2 * self._cap)
+        mine = []
+        if ok:
+            try:
+                for _ in range(2):
+                    ptr = ctypes.c_void_p(); h = (ctypes.c_ubyte * 64)()
+                    if lib.rg_ipc_alloc(nbytes, ctypes.byref(ptr), h) != 0:
+                        raise RuntimeError("rg_ipc_alloc")
+                    mine.append((ptr.value, bytes(h)))
+            except Exception:
+                ok = False
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, mine if ok else None, group=self.group)
+        if not all(e is not None and len(e) == 2 for e in everyone):
+            for ptr, _ in mine:
+                lib.rg_ipc_free(ctypes.c_void_p(ptr))
+            return
+        peers, handles = [], []
+        try:
+            for k in range(2):
+                addrs, opened = [], []
+                for r in range(self.world):
+                    if r == self.rank:
+                        addrs.append(mine[k][0]); continue
+                    p = ctypes.c_void_p(); hb = (ctypes.c_ubyte * 64).from_buffer_copy(everyone[r][k][1])
+                    if lib.rg_ipc_open(hb, ctypes.byref(p)) != 0:
+                        raise RuntimeError("rg_ipc_open")
+                    addrs.append(p.value); opened.append(p.value)
+                table = torch.tensor(addrs, dtype=torch.int64, device=self.device)
+                peers.append((ctypes.c_void_p(mine[k][0]), table)); handles.append((mine[k][0], table, opened))
+            good = 1
+        except Exception:
+            good = 0
+        flag = torch.tensor([good], dtype=torch.int32, device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        self._peer_handles = handles
+        if int(flag.item()) == 1:
+            self._peers = peers
+            self._meet = torch.zeros(1, dtype=torch.int32, device=self.device)
+        else:
+            self._release_peer_buffers()
+
     # ---- the grow
     def _mark(self, name):
         """optional segment timing (RG_SLAB_TIMING=1): CUDA events on the current stream + host clock"""
@@ -147,7 +206,22 @@ class SlabGrower:
                                    self.seeds_dev.data_ptr() if self.nseeds else None, self.nseeds, int(threshold),
                                    self.mask.data_ptr(), st), "rg_slab_label")
         self._mark("label")
-        if self.world > 1 and optimistic and self._cap:
+        if self.world > 1 and optimistic and self._cap and self._peers:
+            # no gather: every rank exports into a buffer its peers have mapped (CUDA IPC), one tiny all-reduce is the barrier
+            # ("all exports are complete"), and the resolve kernels read the other ranks' lists over NVLink where they lie
+            torch, dist = self.torch, self.dist
+            cap = self._cap
+            own, table = self._peers[self._peer_turn]
+            self._peer_turn ^= 1                             # two buffers: a fast rank may export step k+1 while a slow one reads step k
+            self._ck(lib.rg_slab_export_packed(self.ctx, own, cap, st), "rg_slab_export_packed")
+            self._mark("export")
+            dist.all_reduce(self._meet, group=self.group)
+            self._mark("gather_lists")
+            self._ck(lib.rg_slab_resolve_peers(self.ctx, self._xpar.data_ptr(), self._xpar_cap, table.data_ptr(), cap,
+                                               self.rank, self.world, st), "rg_slab_resolve_peers")
+            self._mark("resolve")
+            self.optimistic_steps += 1
+        elif self.world > 1 and optimistic and self._cap:
             torch, dist = self.torch, self.dist
             cap = self._cap
             self._ck(lib.rg_slab_export_packed(self.ctx, self._packed.data_ptr(), cap, st), "rg_slab_export_packed")
@@ -195,6 +269,7 @@ class SlabGrower:
                 self._packed = torch.zeros(4 + 2 * self._cap, dtype=torch.int32, device=self.device)
                 self._allpacked = torch.zeros(self.world * (4 + 2 * self._cap), dtype=torch.int32, device=self.device)
                 self._xpar = torch.empty(self._xpar_cap, dtype=torch.int32, device=self.device)
+                self._map_peer_buffers()
             self.rounds = 1
         self._ck(lib.rg_slab_finish(self.ctx, st), "rg_slab_finish")
         self._mark("finish")
