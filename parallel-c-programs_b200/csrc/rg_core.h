@@ -35,7 +35,7 @@ enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, C
 /* CTR_NCOMPLEX: tiles listed for the full labelling pass; CTR_NDENSE: tiles the in-CTA dense path labelled (rg_dense.h);
    CTR_NPLANES: link-plane slots handed out (both of those passes keep a tile's planes for pass C);
    CTR_NROWTILES: tiles of constant rows labelled at row granularity (rg_rows.h); CTR_NROWOUT: those of them that hold region
-   voxels (listed from the END of flag_list downwards for the row output kernel) */
+   voxels (statistics; the row tiles themselves are listed from the END of flag_list downwards for the row output kernel) */
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
 
 /* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
@@ -774,7 +774,7 @@ struct RowsOutSmem {
 /* pass C for a tile of constant rows (rg_rows.h): the flood runs over TY x TZ row bits -- word z holds the rows of plane z,
    its links along y are the bits of ly[z] (closed with the same carry trick as a voxel word), lz[z] joins planes z and z+1 */
 template <class C, class S, class Exec>
-RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, const TileRec &rc, int64_t x0, int64_t y0, int64_t z0)
+RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, uint32_t tile, const TileRec &rc, int64_t x0, int64_t y0, int64_t z0)
 {
     uint32_t *ly = s.ex, *lz = s.ex + C::TZ, *M = s.M;
     const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;
@@ -790,7 +790,11 @@ RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, const TileRec &rc, 
         }
     });
     ex.sync();
-    if (!s.scal[SC_ANY]) { zero_tile<C>(ex, P, x0, y0, z0); return; }
+    if (ex.tid() == 0) {                                          /* the flag pass leaves row tiles to this function */
+        P.rec[tile].has_region = s.scal[SC_ANY] ? 1 : 0;
+        if (s.scal[SC_ANY]) atomic_add(&P.counters[CTR_NROWOUT], 1u);
+    }
+    if (!s.scal[SC_ANY]) { if (!P.mask_prezeroed) zero_tile<C>(ex, P, x0, y0, z0); return; }
     for (;;) {
         bool changed = false;
         ex.pfor(C::TZ, [&](int z) {
@@ -820,7 +824,7 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
     const TileRec rc = P.rec[tile];
 
     if (rc.nnodes == 0) { zero_tile<C>(ex, P, x0, y0, z0); return; }
-    if (rc.uniform == 2) { tile_pass_c_rows<C>(ex, P, s, rc, x0, y0, z0); return; }
+    if (rc.uniform == 2) { tile_pass_c_rows<C>(ex, P, s, tile, rc, x0, y0, z0); return; }
     const bool saved = P.planes && rc.plane_slot1;                  /* the full pass kept this tile's link planes */
     if (saved) {
         const uint32_t *src = P.planes + (size_t)(rc.plane_slot1 - 1u) * 3 * C::NW;

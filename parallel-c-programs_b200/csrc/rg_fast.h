@@ -452,16 +452,14 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
     const uint32_t ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
     ex.wfor(ntiles,
         [&](uint32_t tile, uint32_t lane) -> bool {
+            if (P.rec[tile].uniform == 2) return false;              /* row tiles: decided and written by the row output kernel */
             const uint32_t nn = P.rec[tile].nnodes, nb = P.rec[tile].node_base;
             for (uint32_t i = lane; i < nn; i += FLAG_LANES) if (find32(P.nparent, nb + i) == 0u) return true;
             return false;
         },
         [&](uint32_t tile, uint32_t lane, bool mine) {
+            if (P.rec[tile].uniform == 2) return;
             if (lane == 0) P.rec[tile].has_region = mine ? 1 : 0;
-            if (mine && P.rec[tile].uniform == 2) {                  /* a row tile: the light output kernel, listed from the end */
-                if (lane == 0) P.flag_list[ntiles - 1u - atomic_add(&P.counters[CTR_NROWOUT], 1u)] = tile;
-                return;
-            }
             if (mine && P.rec[tile].uniform != 1) {
                 if (lane == 0) P.flag_list[atomic_add(&P.counters[CTR_NFLAGGED], 1u)] = tile;
                 return;
@@ -477,11 +475,11 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
 template <class C, class Exec>
 RG_FN void rows_out_list(Exec &ex, const Params &P, RowsOutSmem<C> &s)
 {
-    const uint32_t n = P.counters[CTR_NROWOUT], ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
+    const uint32_t n = P.counters[CTR_NROWTILES], ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
     for (uint32_t i = ex.bid(); i < n; i += ex.nblk()) {
         const uint32_t tile = P.flag_list[ntiles - 1u - i];
         int tx, ty, tz; tile_origin<C>(P, tile, tx, ty, tz);
-        tile_pass_c_rows<C>(ex, P, s, P.rec[tile], (int64_t)tx * C::TX, (int64_t)ty * C::TY, (int64_t)tz * C::TZ);
+        tile_pass_c_rows<C>(ex, P, s, tile, P.rec[tile], (int64_t)tx * C::TX, (int64_t)ty * C::TY, (int64_t)tz * C::TZ);
         ex.sync();
     }
 }

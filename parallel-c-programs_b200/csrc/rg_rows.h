@@ -140,7 +140,10 @@ RG_FN void tile_label_rows(Exec &ex, const Params &P, uint32_t tile, S &s, int v
         for (int f = 0; f < 6; f++) rc.cnt[f] = (uint16_t)s.scal[SC_CNT0 + f];
         rc.uniform = 2; rc.has_region = 0; rc.plane_slot1 = s.scal[SC_PLANE1]; rc.pad3 = 0;
         P.rec[tile] = rc;
-        atomic_add(&P.counters[CTR_NROWTILES], 1u);
+        /* row tiles get their own work list (from the end of the pass C list downwards): the row output kernel decides by itself
+           whether the tile holds region voxels, the flag pass skips them */
+        const uint32_t ntiles = (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz;
+        P.flag_list[ntiles - 1u - atomic_add(&P.counters[CTR_NROWTILES], 1u)] = tile;
     }
 }
 
