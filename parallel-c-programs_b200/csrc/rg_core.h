@@ -131,6 +131,17 @@ struct Params {
     int32_t debug_stop;          /* tuning aid (env RG_DEBUG_STOP): fast pass returns after phase k; results are then invalid */
 };
 
+/* Link-plane slot of a tile (+ 1; 0 = none).  With a slot for every tile -- volumes up to 64 Ki tiles -- the slot is the tile index:
+   no counter, nothing to wait for.  Otherwise slots are handed out by a counter to the tiles that ask (one thread per tile calls this). */
+RG_FN uint32_t plane_slot1(const Params &P, uint32_t tile)
+{
+    if (!P.planes) return 0u;
+    if (P.plane_cap >= (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz) return tile + 1u;
+    const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u);
+    return slot < P.plane_cap ? slot + 1u : 0u;
+}
+RG_FN bool plane_slot_is_tile(const Params &P) { return P.planes && P.plane_cap >= (uint32_t)P.ntx * (uint32_t)P.nty * (uint32_t)P.ntz; }
+
 /* which axis a multi-GPU slab is cut along: z for volumes, y (rows) for images (tiles without a z halo) */
 template <class C> RG_HDFN int ext_zlo(const Params &P) { return C::HZ ? P.lo_ext : 0; }
 template <class C> RG_HDFN int ext_zhi(const Params &P) { return C::HZ ? P.hi_ext : 0; }
@@ -611,9 +622,7 @@ RG_FN void tile_pass_a(Exec &ex, const Params &P, uint32_t tile, TileSmem<C> &s)
         int a = lo; hi = P.nseeds;
         while (lo < hi) { int mid = (lo + hi) >> 1; if (P.seed_keys[mid] < hi_key) lo = mid + 1; else hi = mid; }
         s.scal[SC_SEED_LO] = (uint32_t)a; s.scal[SC_SEED_HI] = (uint32_t)lo; s.scal[SC_OVERFLOW] = 0; s.scal[SC_UNIFORM] = 0;
-        uint32_t p1 = 0;                                        /* a slot for this tile's link planes (shared with the dense path) */
-        if (P.planes) { const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u); if (slot < P.plane_cap) p1 = slot + 1u; }
-        s.scal[SC_PLANE1] = p1;
+        s.scal[SC_PLANE1] = plane_slot1(P, tile);              /* a slot for this tile's link planes (shared with the dense path) */
     }
     if (!ex.template tma_tile<C>(P, s.u.i.img, &s.mbar, x0, y0, z0)) load_tile<C>(ex, P, s.u.i.img, x0, y0, z0, true);
     ex.tile_wait(&s.mbar);

@@ -272,9 +272,7 @@ RG_FN bool tile_label_dense(Exec &ex, const Params &P, uint32_t tile, S &s, int6
     uint32_t rx[NPT], ry[NPT], rz[NPT];
     ex.pfor_k(C::NW, [&](int i, int k) { link_words<C>(P, s.u.img, dense_word<C>(i), x0, vy, vz, rx[k], ry[k], rz[k]); });
     if (ex.tid() == 0) {
-        uint32_t p1 = 0;
-        if (P.planes) { const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u); if (slot < P.plane_cap) p1 = slot + 1u; }
-        s.scal[SC_PLANE1] = p1;
+        s.scal[SC_PLANE1] = plane_slot1(P, tile);
     }
     ex.sync();                                               /* every thread is done with the staged bytes */
     {

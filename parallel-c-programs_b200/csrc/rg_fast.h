@@ -314,12 +314,12 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
     uint32_t nnodes;
     if (rows) {
         /* needs a link-plane slot for its row links; without one (more such tiles than slots) it is labelled like any other tile */
-        if (ex.tid() == 0) {
-            const uint32_t slot = atomic_add(&P.counters[CTR_NPLANES], 1u);
-            s.scal[SC_PLANE1] = slot < P.plane_cap ? slot + 1u : 0u;
+        if (plane_slot_is_tile(P)) { if (ex.tid() == 0) s.scal[SC_PLANE1] = tile + 1u; }       /* read after later barriers only */
+        else {
+            if (ex.tid() == 0) s.scal[SC_PLANE1] = plane_slot1(P, tile);
+            ex.sync();
+            rows = s.scal[SC_PLANE1] != 0;
         }
-        ex.sync();
-        rows = s.scal[SC_PLANE1] != 0;
     }
     if (rows) {
         if (RowsCfg<C>::OK) tile_label_rows<C>(ex, P, tile, s, vy, vz);
