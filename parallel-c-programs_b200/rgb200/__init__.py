@@ -82,7 +82,11 @@ def bind(lib, names=None):
     for name, (res, args) in SIGNATURES.items():
         if names is not None and name not in names:
             continue
-        fn = getattr(lib, name)
+        fn = getattr(lib, name, None)
+        if fn is None:
+            if os.environ.get("RG_LIB"):                     # tuning: an older build may lack the newest entry points
+                continue
+            raise RGError(f"{LIB_PATH} does not export {name}")
         fn.restype = res
         fn.argtypes = args
     return lib
