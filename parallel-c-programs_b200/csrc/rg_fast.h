@@ -198,6 +198,26 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const
         if (m) fmask[C::fw_off(f) + o * C::WX + wx] = dedupe(m, xedges_within(a, tmode, t4), xedges_within(b, tmode, t4));
     });
     /* x faces: one bit per (y, z) */
+#if RG_DEVICE_BUILD
+    if (C::TY == 32) {
+        /* a warp per (side, plane): lane = row, the 32 verdicts are one mask word -- no index arithmetic, no atomics */
+        const int lane = ex.tid() & 31, nwarp = Exec::NTHREADS / 32;
+        for (int wi = ex.tid() >> 5; wi < 2 * C::TZ; wi += nwarp) {
+            const int side = wi / C::TZ, z = wi % C::TZ, y = lane, q = z * C::TY + y;
+            const bool seam = side ? open_xp : open_xm;
+            if (!seam && (side ? !has_xp : !has_xm)) continue;               /* the same for the whole warp */
+            bool e = false;
+            if (y < vy && z < vz) {
+                const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
+                const uint32_t own = o[0], other = side ? (C::XR ? o[1] : xr[q]) : o[-1];
+                e = seam || absdiff(own, other) < P.thr;
+            }
+            const uint32_t m = __ballot_sync(0xFFFFFFFFu, e);
+            if (lane == 0 && m) fmask[C::fw_off(side ? F_XP : F_XM) + z] = m;
+        }
+        return;
+    }
+#endif
     ex.pfor(2 * C::TY * C::TZ, [&](int it) {
         const int side = it / (C::TY * C::TZ), q = it % (C::TY * C::TZ);
         const int y = q % C::TY, z = q / C::TY;
