@@ -370,13 +370,21 @@ RG_FN void build_edges(Exec &ex, const Params &P, const uint8_t *img, uint32_t *
             uint32_t nextvalid = (gx0 + 32 < nx) ? 0x80000000u : 0u;
             uint32_t e = edge_word(a, b, tmode, t4) & vmask & ((vmask >> 1) | nextvalid);
             if (wx == C::WX - 1) {
-                if (FACES && (e >> 31)) { int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XP) + (bi >> 5)], 1u << (bi & 31)); }
+                if (FACES && (e >> 31)) {
+                    /* images: one entry per pair of overlapping y-runs (the same rule as rg_fast.h build_face_masks) */
+                    const uint8_t *pc = rowp + 31;
+                    const bool dup = !C::HZ && y > 0 && similar1(pc[-C::RS], pc[1 - C::RS], tmode, t4) && similar1(pc[0], pc[-C::RS], tmode, t4)
+                                     && similar1(pc[1], pc[1 - C::RS], tmode, t4);
+                    if (!dup) { int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XP) + (bi >> 5)], 1u << (bi & 31)); }
+                }
                 e &= 0x7FFFFFFFu;
             }
             exw = e;
             if (FACES && wx == 0 && x0 > 0 && (vmask & 1u)) {
                 if (similar1(rowp[-1], a[0] & 0xFFu, tmode, t4)) {
-                    int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31));
+                    const bool dup = !C::HZ && y > 0 && similar1(rowp[-1 - C::RS], rowp[-C::RS], tmode, t4) && similar1(rowp[0], rowp[-C::RS], tmode, t4)
+                                     && similar1(rowp[-1], rowp[-1 - C::RS], tmode, t4);
+                    if (!dup) { int bi = z * C::TY + y; atomic_or(&fmask[C::fw_off(F_XM) + (bi >> 5)], 1u << (bi & 31)); }
                 }
             }
             /* +y */

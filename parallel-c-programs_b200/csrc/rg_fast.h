@@ -225,7 +225,15 @@ RG_FN void build_face_masks(Exec &ex, const Params &P, const uint8_t *img, const
         if ((!seam && (side ? !has_xp : !has_xm)) || y >= vy || z >= vz) return;
         const uint8_t *o = img + img_off<C>(side ? C::TX - 1 : 0, y, z);
         const uint32_t own = o[0], other = side ? (C::XR ? o[1] : xr[q]) : o[-1];       /* lean layout: the x = TX column is in xr */
-        if (seam || absdiff(own, other) < P.thr) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
+        bool e = seam || absdiff(own, other) < P.thr;
+        if (!C::HZ && e && !seam && y > 0) {
+            /* images (tiles 126 rows high): one entry per pair of overlapping y-runs, the way the y faces keep one per pair of x-runs --
+               redundant if the row above has an edge too and both columns continue from there to here; both tiles see the same four
+               pixels.  (For volumes the same rule costs the labelling pass more than it saves the merge: measured, left out.) */
+            const uint32_t own1 = o[-C::RS], other1 = side ? o[1 - C::RS] : o[-1 - C::RS];
+            if (absdiff(own1, other1) < P.thr && absdiff(own, own1) < P.thr && absdiff(other, other1) < P.thr) e = false;
+        }
+        if (e) atomic_or(&fmask[C::fw_off(side ? F_XP : F_XM) + (q >> 5)], 1u << (q & 31));
     });
 }
 
