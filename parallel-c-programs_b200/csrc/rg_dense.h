@@ -122,7 +122,10 @@ RG_FN void dense_label_runs(Exec &ex, const Params &P, uint32_t tile, S &s, PT *
        (or of C3's background) would all hook under the row above in the same instant: chains as long as the tile is high,
        which every later find walks.  A thread that works through SEG consecutive rows (then planes) finds the tree it has
        just extended already flat, so chains grow by one per SEG rows instead of one per row. */
-    constexpr int SEG = 4;
+#ifndef RG_DENSE_SEG
+#define RG_DENSE_SEG 4
+#endif
+    constexpr int SEG = RG_DENSE_SEG;
     constexpr int NYSEG = (C::TY + SEG - 1) / SEG, NZSEG = (C::TZ + SEG - 1) / SEG;
     ex.pfor(C::WX * NYSEG * C::TZ, [&](int it) {
         const int wx = it % C::WX, ys = (it / C::WX) % NYSEG, z = it / (C::WX * NYSEG);
