@@ -37,6 +37,9 @@ enum { CTR_NODES = 0, CTR_STATUS = 1, CTR_FACE_MISMATCH = 2, CTR_NCOMPLEX = 3, C
    CTR_NROWTILES: tiles of constant rows labelled at row granularity (rg_rows.h); CTR_NROWOUT: those of them that hold region
    voxels (statistics; the row tiles themselves are listed from the END of flag_list downwards for the row output kernel) */
 enum { ST_NODE_OVERFLOW = 1u, ST_FACE_MISMATCH = 2u };
+/* top bit of a face-list entry: the node is a single voxel with this one cross-tile edge and no seed.  Two such nodes facing each
+   other are a closed component of two voxels: never part of the region, so the merge skips the pair.  Node ids are below 2^15. */
+enum { ENT_LEAF = 0x8000u };
 
 /* XR_: bytes staged to the right of the tile.  16 (the default) brings the x = TX halo byte along in the TMA box; 0 is
    the lean layout of the fast labelling pass, which fetches that one column by itself and gains a fourth CTA per SM. */
@@ -727,7 +730,9 @@ RG_FN void merge_faces(Exec &ex, const Params &P)
             /* faces inside a solid list the same pair of nodes hundreds of times: a lane skips a pair it has just united */
             uint32_t pa = 0xFFFFFFFFu, pb = 0xFFFFFFFFu, qa = 0xFFFFFFFFu, qb = 0xFFFFFFFFu;      /* the last two pairs: C3's faces alternate corridor / background */
             for (uint32_t i = lane; i < cnt; i += MERGE_LANES) {
-                const uint32_t a = ra.node_base + ea[i], b = rb.node_base + eb[i];
+                const uint32_t ar = ea[i], br = eb[i];
+                if (ar & br & ENT_LEAF) continue;
+                const uint32_t a = ra.node_base + (ar & (ENT_LEAF - 1u)), b = rb.node_base + (br & (ENT_LEAF - 1u));
                 if ((a == pa && b == pb) || (a == qa && b == qb)) continue;
                 unite32(P.nparent, a, b);
                 qa = pa; qb = pb; pa = a; pb = b;

@@ -38,6 +38,7 @@ struct DenseCfg {
     static constexpr int ROOM = (C::IMG_BYTES - 16 * C::NW) / 2;
     static constexpr int CAP = C::HZ ? (ROOM < C::NV ? (ROOM > 64 ? ROOM / 8 * 8 : 64) : C::NV) : C::NV;
     static constexpr int CAPW = (CAP + 31) / 32;             /* words of a bit set over run ids */
+    static_assert(CAP < (int)ENT_LEAF, "node ids in the face lists stay below the ENT_LEAF bit");
     /* once the unions are done the +y / +z planes are dead: the open / seeded bit sets and the node prefix
        (4 + 4 + 2 bytes per 32 ids) move in if they fit */
     static constexpr bool ALIAS_POST = 10 * CAPW <= 8 * C::NW;

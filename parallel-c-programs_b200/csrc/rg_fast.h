@@ -371,7 +371,13 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         ex.pfor((int)etot, [&](int e) {
             const uint32_t v = s.ent_root[e];
             if (neighbour_mask<C>(s.u.img, vx, vy, vz, P.thr, v)) s.v.e.u.slow[atomic_add(&s.scal[SC_NSLOW], 1u)] = (uint16_t)e;
-            else s.ent_root[e] = (uint16_t)hash_slot(s.tab, s.scal, v);
+            else {
+                /* a voxel with no similar neighbour inside the tile that lies on ONE face has exactly this one edge: if its partner on
+                   the other side is of the same kind the two form a closed pair, and the merge need not look at them (ENT_LEAF) */
+                const int x = (int)(v % C::TX), y = (int)((v / C::TX) % C::TY), z = (int)(v / (C::TX * C::TY));
+                const int onfaces = (x == 0) + (x == C::TX - 1) + (y == 0) + (y == vy - 1) + (C::HZ ? (z == 0) + (z == vz - 1) : 0);
+                s.ent_root[e] = (uint16_t)(hash_slot(s.tab, s.scal, v) | (onfaces == 1 ? (uint32_t)ENT_LEAF : 0u));
+            }
         });
         {
             const int lo = (int)s.scal[SC_SEED_LO], hi = (int)s.scal[SC_SEED_HI];
@@ -420,7 +426,12 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
             return;
         }
         /* face lists and nodes go out in one sweep */
-        ex.pfor((int)etot, [&](int e) { ent[e] = s.v.slotid[s.ent_root[e]]; });
+        ex.pfor((int)etot, [&](int e) {
+            const uint32_t r = s.ent_root[e], slot = r & (ENT_LEAF - 1u);
+            uint32_t id = s.v.slotid[slot];
+            if ((r & ENT_LEAF) && !((s.seedtab[slot >> 5] >> (slot & 31)) & 1u)) id |= ENT_LEAF;      /* a seeded voxel is never a closed pair */
+            ent[e] = (uint16_t)id;
+        });
         ex.pfor(HASH_N, [&](int slot) {
             const uint32_t cur = s.tab[slot];
             if (!cur) return;

@@ -61,7 +61,7 @@ RG_FN void export_entries(Exec &ex, const Params &P, int side, const uint32_t *t
         uint32_t *o = out_roots + tile_off[i];
         const uint32_t first = tile_off[i];
         for (uint32_t k = lane; k < cnt; k += EXPORT_LANES)
-            if (first + k < cap) o[k] = find32(P.nparent, rc.node_base + e[k]);      /* a list longer than the buffer is reported, not written */
+            if (first + k < cap) o[k] = find32(P.nparent, rc.node_base + (e[k] & (ENT_LEAF - 1u)));      /* a list longer than the buffer is reported, not written */
     });
 }
 
@@ -96,7 +96,7 @@ RG_FN void export_border(Exec &ex, const Params &P, int side, uint32_t *out_root
         const uint32_t idx = (uint32_t)(side < 2 ? y % C::TY : x % C::TX);      /* every valid border pixel is an entry, in order */
         uint32_t r = 1u;                                            /* (a valid vertex, should the self-check below ever fire) */
         if (P.tmode == 0) r = 0u;                                   /* threshold <= 0: no pixel is similar to any other, nothing to exchange */
-        else if (idx < rc.cnt[f]) r = find32(P.nparent, rc.node_base + P.ent[(size_t)tile * C::ENT_MAX + off + idx]);
+        else if (idx < rc.cnt[f]) r = find32(P.nparent, rc.node_base + (P.ent[(size_t)tile * C::ENT_MAX + off + idx] & (ENT_LEAF - 1u)));
         else atomic_or(&P.counters[CTR_STATUS], ST_FACE_MISMATCH);
         out_roots[i] = r;
         out_vals[i] = P.image[y * P.nx + x];
