@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(256) k_region_boxes(const Params P, int32_t *o
 }
 
 template <class C>
-__global__ void __launch_bounds__(256) k_merge(const Params P)
+__global__ void __launch_bounds__(256, 8) k_merge(const Params P)      /* latency bound: all 64 warps of an SM */
 {
     DevExec<256> ex;
     merge_faces<C>(ex, P);
