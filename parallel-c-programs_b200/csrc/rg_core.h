@@ -824,7 +824,7 @@ RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, uint32_t tile, cons
     ex.sync();
     ex.pfor((int)rc.nnodes, [&](int i) {
         const uint32_t g = rc.node_base + (uint32_t)i;
-        if (find32(P.nparent, g) == 0u) {
+        if ((P.debug_stop == 31 || P.debug_stop == 32) ? (g & 1u) != 0u : find32(P.nparent, g) == 0u) {      /* tuning: 31 / 32 time the output without the finds */
             const uint32_t r = (uint32_t)P.nrep[g] / (uint32_t)C::TX;
             atomic_or(&M[r / C::TY], 1u << (r % C::TY));
             s.scal[SC_ANY] = 1;
@@ -847,9 +847,14 @@ RG_FN void tile_pass_c_rows(Exec &ex, const Params &P, S &s, uint32_t tile, cons
         });
         if (!ex.sync_or(changed)) break;
     }
+    if (P.debug_stop == 30 || P.debug_stop == 32) return;              /* tuning: ... and without the stores */
+    /* Stores alone drain at 3.9 TB/s on this part (a copy moves 6.6: half of it reads), and the labelling pass has cleared the
+       tile already: only the rows of ones are written (C3: a quarter of the bytes, row output 0.35 -> ... ms). */
+    const bool ones_only = P.mask_prezeroed != 0;
     ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
         const int r = it / C::CX, y = r % C::TY, z = r / C::TY;
-        fill_chunk<C>(P, x0, y0, z0, (M[z] >> y) & 1u, it);
+        const uint32_t bit = (M[z] >> y) & 1u;
+        if (bit | (uint32_t)!ones_only) fill_chunk<C>(P, x0, y0, z0, bit, it);
     });
 }
 
@@ -910,6 +915,7 @@ RG_FN void tile_pass_c(Exec &ex, const Params &P, uint32_t tile, FloodSmem<C> &s
         int64_t gx = x0 + 16 * c, gy = y0 + y, gz = z0 + z;
         if (gy >= P.ny || gz >= P.nz || gx >= P.nx) return;
         uint32_t bits = (s.M[(z * C::TY + y) * C::WX + (c >> 1)] >> ((c & 1) * 16)) & 0xFFFFu;
+        if (!bits && P.mask_prezeroed) return;                       /* cleared by the labelling pass: zeros are not stored twice */
         u32x4 v = { expand4(bits & 15u), expand4((bits >> 4) & 15u), expand4((bits >> 8) & 15u), expand4(bits >> 12) };
         uint8_t *g = P.mask + (gz * P.ny + gy) * P.nx + gx;
         if (P.fast16) st128_stream(g, v);
