@@ -254,9 +254,16 @@ __global__ void __launch_bounds__(RG_PASSC_THREADS, 3) k_pass_c(const Params P, 
     pass_c_list<L>(ex, P, s);
 }
 
-/* pass C for tiles of constant rows: no staging, a few words of shared memory, many CTAs per SM */
-#define RG_ROWS_THREADS 128
-#define RG_ROWS_CTAS (148 * 12)
+/* pass C for tiles of constant rows: no staging, a few words of shared memory.  A tile is a chain of dependent loads (list, record,
+   link words, finds) and then a few stores: as many tiles in flight as an SM takes -- 32 CTAs of two warps (C3, row output +
+   pass C: 0.350 ms with 12 x 128 threads, 0.326 with 16 x 128, 0.308 with 32 x 64) */
+#ifndef RG_ROWS_THREADS
+#define RG_ROWS_THREADS 64
+#endif
+#ifndef RG_ROWS_PER_SM
+#define RG_ROWS_PER_SM 32
+#endif
+#define RG_ROWS_CTAS (148 * RG_ROWS_PER_SM)
 template <class C>
 __global__ void __launch_bounds__(RG_ROWS_THREADS) k_rows_out(const Params P)
 {

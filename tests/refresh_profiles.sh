@@ -9,12 +9,12 @@ S="python3 tests/summarise_ncu.py"
   echo "Algorithmic bytes of this kernel per launch: 2 B x 2048^3 = 17.18 GB (reads every voxel once, clears every mask byte once)."; echo
   $S gpurun_out/r02_fast_c4.ncu-rep; } > profiles/r02_ncu_pass_a_fast_C4.md
 { echo "# Round 2 -- ncu evidence, merge / flag / pass C on C4 2048^3"; echo
-  echo "Same command as r02_ncu_pass_a_fast_C4.md, \`-k regex:\"k_merge|k_pass_c|k_flag_tiles\" --launch-skip 3 --launch-count 3\`. Build: commit $H."; echo
+  echo "Same command as r02_ncu_pass_a_fast_C4.md, \`-k regex:\"k_merge|k_pass_c|k_flag_tiles|k_rows_out\" --launch-skip 4 --launch-count 4\`. Build: commit $H."; echo
   cat profiles/notes_r02_rest_c4.txt 2>/dev/null; echo
   $S gpurun_out/r02_rest_c4.ncu-rep; } > profiles/r02_ncu_merge_flag_passc_C4.md
 for wl in C3 C1 C2; do
   { echo "# Round 2 -- ncu evidence, the kernels of one grow on $wl"; echo
-    echo "Command (exited 0 without ncu first): \`python bench.py --no-extras --steps 2 --warmup 1 --workload $wl\`, then \`ncu --set full --clock-control none --import-source on -k regex:\"k_pass_a_fast|k_merge|k_pass_c|k_flag_tiles\" --launch-skip 4 --launch-count 4\`. Build: commit $H."
+    echo "Command (exited 0 without ncu first): \`python bench.py --no-extras --steps 2 --warmup 1 --workload $wl\`, then \`ncu --set full --clock-control none --import-source on -k regex:\"k_pass_a_fast|k_merge|k_pass_c|k_flag_tiles|k_rows_out\" --launch-skip n --launch-count n\` (n = 5 kernels of one step; 4 for the image C2). Build: commit $H."
     cat profiles/notes_r02_$wl.txt 2>/dev/null; echo
     $S gpurun_out/r02_all_$wl.ncu-rep; } > profiles/r02_ncu_$wl.md
 done
