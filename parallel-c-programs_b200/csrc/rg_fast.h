@@ -486,6 +486,12 @@ RG_FN void flag_tiles_all(Exec &ex, const Params &P)
         [&](uint32_t tile, uint32_t lane) -> bool {
             if (P.rec[tile].uniform == 2) return false;              /* row tiles: decided and written by the row output kernel */
             const uint32_t nn = P.rec[tile].nnodes, nb = P.rec[tile].node_base;
+            /* tuning: 40 = the pass without its finds, 41 = with one plain load per node instead.  Both take 0.025 ms on C4 where the
+               pass takes 0.31 (0.07 of it the ones of the uniform region tiles): the time is the SECOND step of the finds, a scattered
+               sector per node that has a parent.  Four first steps in flight per lane, cached or gpu-scope loads instead of
+               volatile ones, finds without path compression: each was measured and none is faster. */
+            if (P.debug_stop == 40) return false;
+            if (P.debug_stop == 41) { uint32_t acc = 1u; for (uint32_t i = lane; i < nn; i += FLAG_LANES) acc &= P.nparent[nb + i]; return acc == 0xFFFFFFFFu; }
             for (uint32_t i = lane; i < nn; i += FLAG_LANES) if (find32(P.nparent, nb + i) == 0u) return true;
             return false;
         },
