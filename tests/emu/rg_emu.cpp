@@ -61,6 +61,8 @@ static int g_no_planes = 0;      /* 1: label every tile with the full pass (fast
 static int g_force_dense = 0;    /* 1: every non-uniform tile takes the dense path of the fast pass */
 static int g_no_rows = 0;        /* 1: tiles of constant rows are labelled like any other tile */
 static uint32_t g_last_dense = 0, g_last_full = 0, g_last_rows = 0;
+static int g_no_prezero = 0;     /* 1: the labelling pass leaves the mask alone (the library's RG_NO_PREZERO): the later passes write every byte */
+extern "C" void emu_no_prezero(int v) { g_no_prezero = v; }
 extern "C" void emu_no_rows(int v) { g_no_rows = v; }
 extern "C" uint32_t emu_last_rows(void) { return g_last_rows; }
 extern "C" void emu_force_dense(int v) { g_force_dense = v; }
@@ -84,7 +86,7 @@ static void emu_setup(EmuState &E, const uint8_t *image, int64_t nx, int64_t ny,
     P.ntx = (int)((nx + C::TX - 1) / C::TX); P.nty = (int)((ny + C::TY - 1) / C::TY); P.ntz = (int)((nz + C::TZ - 1) / C::TZ);
     P.lo_ext = zlo; P.hi_ext = zhi;
     P.tmode = T <= 0 ? 0 : T >= 256 ? 2 : 1; P.t4 = (uint32_t)(T & 0xFF) * 0x01010101u; P.thr = T <= 0 ? 0u : T >= 256 ? 256u : (uint32_t)T;
-    P.mask_prezeroed = g_force_full ? 0 : 1;
+    P.mask_prezeroed = (g_force_full || g_no_prezero) ? 0 : 1;
     P.force_dense = g_force_dense;
     P.no_rows = g_no_rows;
     P.fast16 = (nx % 16 == 0) && (((uintptr_t)image & 15) == 0) && (((uintptr_t)mask & 15) == 0);

@@ -339,6 +339,31 @@ def test_emu_row_tiles(emu, oracle, cfg):
     assert (got == oracle.grow(img3, s3, T3)).all() and emu.emu_last_rows() > 0
 
 
+@pytest.mark.parametrize("cfg", [1, 2])
+def test_emu_output_with_and_without_a_cleared_mask(emu, oracle, cfg):
+    """The labelling pass clears each tile's part of the mask, so the output passes store only the chunks / rows that hold a one;
+    with the clear switched off (the library's RG_NO_PREZERO) they and the flag pass must write every byte themselves.  Both ways
+    start from a mask full of garbage (run_emu fills it with 7) over every kind of tile: noise, uniform, rows, dense, ragged."""
+    rng = np.random.default_rng(77 + cfg)
+    nz, ny, nx = 22, 45, 208
+    rowval = rng.integers(0, 3, size=(nz, ny, 1), dtype=np.uint8) * 50
+    img = np.broadcast_to(rowval, (nz, ny, nx)).copy()                            # row tiles ...
+    img[:, :, 96:150] = rng.integers(0, 4, size=(nz, ny, 54))                     # ... a noise band ...
+    img[:, 30:, :64] = 120                                                        # ... a solid (uniform tiles and their borders)
+    img[4:9, 2:20, 10:70] = 200
+    seeds = [[0, 0, 0], [5, 35, 3], [12, 5, 5], [100, 7, 3], [nx - 1, ny - 1, nz - 1]]
+    c3, s3, T3 = oracle.synth("c3", 96)
+    for (vol, sd, T) in ((img, seeds, 1), (img, seeds, 60), (c3, s3, T3)):
+        want = oracle.grow(vol, sd, T)
+        got, _ = run_emu(emu, cfg, vol, sd, T)
+        emu.emu_no_prezero(1)
+        try:
+            got2, _ = run_emu(emu, cfg, vol, sd, T)
+        finally:
+            emu.emu_no_prezero(0)
+        assert (got == want).all() and (got2 == want).all(), (cfg, T)
+
+
 @pytest.mark.parametrize("R,Cn", [(1, 2), (2, 1), (2, 2), (3, 4), (4, 3)])
 @pytest.mark.parametrize("cfg,shape", [(1, (40, 160)), (1, (33, 131)), (0, (260, 530)), (1, (9, 64))])
 def test_emu_image_over_a_grid_of_blocks(emu, oracle, golden, R, Cn, cfg, shape):

@@ -584,6 +584,11 @@ def test_row_tiles_on_gpu(rg, ctx, oracle, monkeypatch):
     want3 = oracle.grow(img3, s3, T3)
     got3 = dev_grow(rg, ctx, img3, s3, T3)
     assert (got3 == want3).all()
+    # the output passes store only the ones of a tile the labelling pass has cleared; with that clear switched off they and the
+    # flag pass have to write every byte (dev_grow hands out a mask full of garbage either way)
+    monkeypatch.setenv("RG_NO_PREZERO", "1")
+    assert (dev_grow(rg, ctx, img3, s3, T3) == want3).all()
+    assert (dev_grow(rg, ctx, img, seeds, 1) == oracle.grow(img, seeds, 1)).all()
 
 
 @pytest.mark.parametrize("R,Cn", [(1, 2), (2, 2), (3, 4), (2, 1)])
