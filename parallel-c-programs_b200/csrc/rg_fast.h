@@ -301,8 +301,12 @@ RG_FN void tile_pass_a_fast(Exec &ex, const Params &P, uint32_t tile, FastSmem<C
         /* the first 16 voxels decide for almost every tile; all threads read the same bytes, so this branch is uniform */
         if (vx >= 16 && ((q0.x ^ pat) | (q0.y ^ pat) | (q0.z ^ pat) | (q0.w ^ pat)) == 0u) {
             bool differs = false, row_differs = false;
+            /* volumes: eight neighbouring lanes read the same 16-byte column of eight consecutive rows -- with rows 80 bytes apart those
+               are eight different groups of four banks, where the four chunks of two neighbouring rows overlap in one */
+            constexpr bool BY_COLUMN = C::CX == 4 && (C::TY * C::TZ) % 8 == 0;
             ex.pfor(C::TZ * C::TY * C::CX, [&](int it) {
-                int c = it % C::CX, r = it / C::CX, y = r % C::TY, z = r / C::TY;
+                const int c = BY_COLUMN ? (it >> 3) & 3 : it % C::CX, r = BY_COLUMN ? (it & 7) | ((it >> 5) << 3) : it / C::CX;
+                const int y = r % C::TY, z = r / C::TY;
                 if (y >= vy || z >= vz || 16 * c >= vx) return;
                 u32x4 q = ld128(&s.u.img[img_off<C>(16 * c, y, z)]);
                 if ((q.x ^ pat) | (q.y ^ pat) | (q.z ^ pat) | (q.w ^ pat)) {

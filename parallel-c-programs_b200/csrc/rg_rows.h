@@ -60,6 +60,21 @@ RG_FN void tile_label_rows(Exec &ex, const Params &P, uint32_t tile, S &s, int v
         if (r < C::TZ) { ly[r] = 0; lz[r] = 0; open[r] = 0; seeded[r] = 0; }
     });
     ex.sync();
+#if RG_DEVICE_BUILD
+    if (C::TY == 32) {
+        /* a warp per plane: lane = row, the 32 verdicts of a plane are one ballot (32 lanes OR-ing bits into one shared word is a
+           31-way conflict: with the plane words of the open bits below, half of this path's excess shared-memory wavefronts on C3) */
+        const int lane = ex.tid() & 31, nwarp = Exec::NTHREADS / 32;
+        for (int z = ex.tid() >> 5; z < C::TZ; z += nwarp) {
+            const int r = z * C::TY + lane;
+            const bool in = lane < vy && z < vz;
+            const bool ey = in && lane + 1 < vy && similar1(val[r], val[r + 1], tmode, t4);
+            const bool ez = in && z + 1 < vz && similar1(val[r], val[r + C::TY], tmode, t4);
+            const uint32_t my = __ballot_sync(0xFFFFFFFFu, ey), mz = __ballot_sync(0xFFFFFFFFu, ez);
+            if (lane == 0) { ly[z] = my; lz[z] = mz; }
+        }
+    } else
+#endif
     ex.pfor(NROWS, [&](int r) {
         const int y = r % C::TY, z = r / C::TY;
         if (y >= vy || z >= vz) return;
@@ -98,12 +113,18 @@ RG_FN void tile_label_rows(Exec &ex, const Params &P, uint32_t tile, S &s, int v
         const int f = (fw >= C::fw_off(1)) + (fw >= C::fw_off(2)) + (fw >= C::fw_off(3)) + (fw >= C::fw_off(4)) + (fw >= C::fw_off(5));
         const int idx = fw - C::fw_off(f);
         uint32_t slot = (uint32_t)fprefix[fw] + (uint32_t)popc(all & ((1u << q8) - 1u));
+        /* neighbouring entries mostly share a root or at least its plane: their bits are collected and OR-ed into the plane's word
+           once, and only if one of them is new (one atomic per entry was a 16-way conflict on every instruction) */
+        uint32_t accw = 0, acc = 0;
         while (m) {
             const int b = ffs1(m) - 1; m &= m - 1;
             const uint32_t r = find16(par, face_voxel<C>(f, idx, b, vy, vz) / (uint32_t)C::TX);
-            atomic_or(&open[r / C::TY], 1u << (r % C::TY));
+            const uint32_t w = r / C::TY;
+            if (w != accw) { if (acc & ~ldv32(&open[accw])) atomic_or(&open[accw], acc); accw = w; acc = 0; }
+            acc |= 1u << (r % C::TY);
             ent[slot++] = (uint16_t)r;
         }
+        if (acc & ~ldv32(&open[accw])) atomic_or(&open[accw], acc);
     });
     const int slo = (int)s.scal[SC_SEED_LO], shi = (int)s.scal[SC_SEED_HI];
     ex.pfor(shi - slo, [&](int i) {
