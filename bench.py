@@ -565,6 +565,10 @@ def main():
                 except Exception as e:
                     others[o] = {"error": repr(e)}
             line["other_workloads"] = others
+            try:
+                line["roofline"]["memory_regimes"] = memory_regimes(torch, dev)
+            except Exception as e:
+                line["roofline"]["memory_regimes"] = {"error": repr(e)}
         if rank == 0 and world == 1:
             L = load_oracle()
             ns = cpu_sample_size(wl)
@@ -589,6 +593,28 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def memory_regimes(torch, dev):
+    """What this GPU moves when a pass only stores and when it copies (torch fill_ / copy_ over 1 GiB, CUDA events, best of 5).  Context for
+    the passes that only write the mask: stores alone drain well below the copy bandwidth the roofline is quoted against."""
+    n = 1 << 30
+    a = torch.empty(n, dtype=torch.uint8, device=dev)
+    b = torch.empty(n, dtype=torch.uint8, device=dev)
+
+    def best(f, reps=5):
+        f()
+        torch.cuda.synchronize(dev)
+        t = []
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); f(); e1.record(); e1.synchronize()
+            t.append(e0.elapsed_time(e1))
+        return min(t)
+    st, cp = best(lambda: a.fill_(1)), best(lambda: b.copy_(a))
+    del a, b
+    return {"store_only_gbs": n / st / 1e6, "copy_gbs": 2 * n / cp / 1e6, "unit": "GB/s",
+            "how": "torch.Tensor.fill_ and copy_ (read + write bytes) over 1 GiB of uint8 on this GPU in this run, best of 5, CUDA events"}
 
 
 def run_e2e(torch, rgb200, lib, ctx, dist, dev, rank, world, wl, n, barrier, max_over_ranks):
