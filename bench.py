@@ -741,9 +741,12 @@ def run_e2e(torch, rgb200, lib, ctx, dist, dev, rank, world, wl, n, barrier, max
                 if rc != 0:
                     raise RuntimeError(lib.rg_last_error().decode())
             sec = float(np.mean(times[1:])) * 1e-3
+            moved = (ctypes.c_int64 * 4)()
+            if lib.rg_multi_stats(moved) != 0:
+                raise RuntimeError(lib.rg_last_error().decode())
             res = {"value": n ** dims / sec / 1e9, "unit": "Gvoxels/s", "ms_per_step": sec * 1e3, "cold_first_call_ms": times[0], "n": n,
-                   "h2d_bytes_per_step": int(h_img.numel() + 2 * (world - 1) * (h_img.numel() // n) + 12 * len(seeds_np)),
-                   "d2h_bytes_per_step": "output-sensitive: only the boxes that hold region voxels (the mask buffer was zeroed once before the loop)",
+                   "h2d_bytes_per_step": int(moved[0]), "d2h_bytes_per_step": int(moved[1]), "d2h_copies": int(moved[2]),
+                   "d2h_note": "output-sensitive: only the boxes that hold region voxels (the mask buffer was zeroed once before the loop); counted by the library (rg_multi_stats)",
                    "region_voxels": int(h_mask.sum(dtype=torch.int64)),
                    "api": f"rg_grow_multi (C ABI, one process, {world} devices): one pinned host image scattered with its halo planes, one peer-copy "
                           "interface exchange, mask gathered into one pinned host buffer",

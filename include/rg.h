@@ -164,6 +164,10 @@ const char *rg_last_error(void);
 #define RG_MULTI_MASK_ZEROED 1
 int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64_t nz, const int32_t *seeds_xyz, int nseeds,
                   int threshold, uint8_t *mask_out, const int *devices, int ndev, int flags, float *phase_ms);
+/* What the last rg_grow_multi of this process moved over PCIe: {host -> device bytes (slabs, boundary planes, seeds), device -> host
+ * bytes, device -> host copies, slabs used} -- the counterpart of rg_host_stats for the multi-device call (region.c:106-246 scatter,
+ * :391-432 gather). */
+int rg_multi_stats(int64_t out[4]);
 
 /* The same for an IMAGE over a rows x cols grid of blocks, the reference's Cartesian process grid (region.c:537-548: MPI_Dims_create /
  * MPI_Cart_create; distribute_image :106-143; the four-border exchange() :250-353; gather_region :391-432): block (i, j) =

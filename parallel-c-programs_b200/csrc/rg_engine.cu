@@ -1417,6 +1417,7 @@ struct MultiSlab {
 };
 static MultiSlab g_multi[RESOLVE_MAX_RANKS];
 static std::mutex g_multi_mu;
+static int64_t g_multi_last[4];                /* last rg_grow_multi: host -> device bytes, device -> host bytes, device -> host copies, slabs */
 
 static int multi_fail(MultiSlab &m, int code) { m.rc = code; snprintf(m.err, sizeof m.err, "%s", g_err); return code; }
 #define MCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(RG_ERR_CUDA, #call, e_); return multi_fail(m, RG_ERR_CUDA); } } while (0)
@@ -1550,8 +1551,27 @@ extern "C" int rg_grow_multi(const uint8_t *image, int64_t nx, int64_t ny, int64
     }
     if (rc == RG_OK) rc = run_all(phase2);
     if (phase_ms) { phase_ms[0] = since(t_start); phase_ms[1] = t1; phase_ms[2] = phase_ms[0] - t1; phase_ms[3] = (float)G; }
+    g_multi_last[0] = g_multi_last[1] = g_multi_last[2] = 0; g_multi_last[3] = G;
+    for (int i = 0; i < nseeds && rc == RG_OK; i++) {                                   /* a seed goes to the slab that owns its plane (row) */
+        const int64_t a = seeds_xyz[3 * i + (rows ? 1 : 2)];
+        if (a >= 0 && a < na) g_multi_last[0] += 12;
+    }
+    for (int g = 0; g < G && rc == RG_OK; g++) {
+        const int64_t z0 = na * g / G, z1 = na * (g + 1) / G;
+        const int64_t lo = z0 > 0 ? 1 : 0, hi = z1 < na ? 1 : 0;                        /* the slab and its neighbours' boundary planes */
+        g_multi_last[0] += (z1 - z0 + lo + hi) * plane;
+        g_multi_last[1] += g_multi[g].ctx->last_d2h_bytes; g_multi_last[2] += g_multi[g].ctx->last_copies;
+    }
     if (prev_dev >= 0) cudaSetDevice(prev_dev);
     return rc;
+}
+
+extern "C" int rg_multi_stats(int64_t out[4])
+{
+    if (!out) return fail(RG_ERR_ARG, "out == NULL");
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    for (int i = 0; i < 4; i++) out[i] = g_multi_last[i];
+    return RG_OK;
 }
 
 /* ------------------------------------------------------------------ one host IMAGE over a rows x columns grid of GPUs

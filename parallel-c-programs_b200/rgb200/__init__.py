@@ -33,6 +33,7 @@ SIGNATURES = {
     "rg_grow": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_grow_sparse": (_i32, [_vp, _i64, _i64, _i64, _vp, _i32, _i32, _vp]),
     "rg_host_stats": (_i32, [_vp]),
+    "rg_multi_stats": (_i32, [_vp]),
     "rg_grow_multi_grid": (_i32, [_vp, _i64, _i64, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _vp]),
     "rg_block_label": (_i32, [_vp, _vp, _i64, _i64, _i32, _vp, _i32, _i32, _vp, _vp]),
     "rg_block_export": (_i32, [_vp, _i32, _vp, _vp, _vp]),

@@ -555,8 +555,15 @@ def test_grow_multi_from_c_abi(rg, oracle, G):
     want = oracle.grow(vol, seeds, 1)
     got, ms = _grow_multi(lib, vol, seeds, 1, devices)
     assert (got == want).all() and int(ms[3]) == G
+    st = (ctypes.c_int64 * 4)()
+    assert lib.rg_multi_stats(st) == 0
+    plane = vol.shape[1] * vol.shape[2]
+    assert st[0] == vol.size + 2 * (G - 1) * plane + 12 * len(seeds)          # every slab with its neighbours' boundary planes, each seed to its slab
+    assert st[1] == vol.size and st[2] >= G and st[3] == G                  # every byte of the mask comes back, at least one copy per slab
     got, _ = _grow_multi(lib, vol, seeds, 1, devices, zeroed=True)
     assert (got == want).all()
+    assert lib.rg_multi_stats(st) == 0
+    assert int(want.sum()) <= st[1] < vol.size and st[2] >= 1               # zeroed mask: only the boxes that hold region voxels
     img, s2, T2 = oracle.synth("c2", 1024, 0x5EED0002)
     got, _ = _grow_multi(lib, img, s2, T2, devices)
     assert (got == oracle.grow(img, s2, T2)).all()
