@@ -390,3 +390,62 @@ def test_emu_image_over_a_grid_of_blocks(emu, oracle, golden, R, Cn, cfg, shape)
         got = np.empty_like(pic); st = np.zeros(4, np.uint32)
         assert emu.emu_grow_grid(0, R, Cn, pic.ctypes.data, 512, 512, s.ctypes.data, 4, 2, got.ctypes.data, st.ctypes.data) == 0
         assert (got == oracle.grow(pic, s, 2)).all() and int(st[2]) == R and int(st[3]) == min(Cn, 4)
+
+
+def _mixed_volume(rng, shape):
+    """noise, constant rows, a solid and a thin line in one volume / image: every labelling path of the fast pass next to every other"""
+    img = rng.integers(0, int(rng.integers(2, 6)), size=shape, dtype=np.uint8)
+    nd = len(shape)
+    if rng.random() < 0.7:                                       # a band of constant rows (row tiles where the band covers whole tiles)
+        rowval = (rng.integers(0, 3, size=shape[:-1] + (1,), dtype=np.uint8) * 40).astype(np.uint8)
+        if rng.random() < 0.5:
+            lo = int(rng.integers(0, shape[-1])); hi = int(rng.integers(lo, shape[-1] + 1))
+        else:                                                    # ... cut on multiples of 32 columns: whole tiles of the tiny tile shapes
+            lo = 32 * int(rng.integers(0, shape[-1] // 32 + 1)); hi = max(lo, 32 * int(rng.integers(0, shape[-1] // 32 + 1)))
+            if rng.random() < 0.5:
+                lo, hi = 0, shape[-1]
+        img[..., lo:hi] = np.broadcast_to(rowval, shape)[..., lo:hi]
+    if rng.random() < 0.7:                                       # a solid box
+        sl = tuple(slice(int(a), int(a) + int(rng.integers(1, max(2, s)))) for s in shape for a in [rng.integers(0, s)])
+        img[sl] = int(rng.integers(100, 255))
+    if rng.random() < 0.5:                                       # a one-voxel line along the first axis
+        idx = tuple(int(rng.integers(0, s)) for s in shape[1:])
+        img[(slice(None),) + idx] = 250
+    return img
+
+
+def test_emu_property_random_mixtures(emu, oracle):
+    """hypothesis over shapes (ragged in every axis), contents, thresholds (<= 0 and > 255 included), seeds (outside the volume and
+    duplicates included), tile shapes, slab counts and the two output modes: always the oracle's bytes"""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=400, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(st.integers(0, 2**31 - 1), st.sampled_from([1, 2]), st.sampled_from([0, 0, 2, 3, 5]), st.booleans(), st.booleans(),
+           st.sampled_from([-3, 0, 1, 1, 2, 5, 41, 255, 256, 1000]))
+    def prop(seed, cfg, slabs, two_d, no_prezero, T):
+        rng = np.random.default_rng(seed)
+        nx = int(rng.integers(1, 150)) if rng.random() < 0.5 else 32 * int(rng.integers(1, 6))       # ragged, or whole tiles and 16-byte rows
+        shape = (int(rng.integers(1, 40)), nx) if two_d else (int(rng.integers(1, 20)), int(rng.integers(1, 30)), nx)
+        img = _mixed_volume(rng, shape)
+        dims = (shape[1], shape[0], 1) if two_d else shape[::-1]
+        k = int(rng.integers(0, 7))
+        seeds = np.stack([rng.integers(-1, d + 1, size=k) for d in dims], 1).astype(np.int32) if k else np.zeros((0, 3), np.int32)
+        if two_d and k:
+            seeds[:, 2] = 0
+        if k > 1:
+            seeds[-1] = seeds[0]
+        want = oracle.grow(img, seeds, T)
+        nslab = slabs if slabs and shape[0] >= slabs else 0
+        emu.emu_no_prezero(1 if no_prezero else 0)
+        try:
+            got, _ = run_emu(emu, cfg, img, seeds, T, slabs=nslab)
+        finally:
+            emu.emu_no_prezero(0)
+        assert (got == want).all(), (seed, cfg, nslab, shape, T, no_prezero)
+        if not nslab:
+            hit["rows"] += emu.emu_last_rows(); hit["dense"] += emu.emu_last_dense(); hit["runs"] += 1
+
+    hit = {"rows": 0, "dense": 0, "runs": 0}
+    emu.emu_last_rows.restype = ctypes.c_uint32; emu.emu_last_dense.restype = ctypes.c_uint32
+    prop()
+    assert hit["runs"] > 50 and hit["rows"] > 0 and hit["dense"] > 0, hit      # the mixtures did reach the row and the dense labelling paths
