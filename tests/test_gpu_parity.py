@@ -632,3 +632,27 @@ def test_grow_multi_grid_from_c_abi(rg, oracle, golden, R, Cn):
     assert (got == oracle.grow(img2, s2, T2)).all()
     got, _ = run(img2, np.zeros((0, 3), np.int32), T2)
     assert not got.any()
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_random_mixtures_on_gpu(rg, ctx, oracle, block):
+    """the emulator's random mixtures (noise, bands of constant rows, solids, thin lines) at the real tile sizes: shapes ragged in every
+    axis or whole tiles, thresholds <= 0 and > 255 included, seeds outside the volume and duplicates included -- always the oracle's bytes"""
+    from test_emu_logic import _mixed_volume
+    rng = np.random.default_rng(0xB200 + block)
+    for case in range(12):
+        two_d = rng.random() < 0.3
+        nx = int(rng.integers(1, 400)) if rng.random() < 0.5 else 64 * int(rng.integers(1, 7))
+        shape = (int(rng.integers(1, 300)), nx) if two_d else (int(rng.integers(1, 50)), int(rng.integers(1, 100)), nx)
+        img = _mixed_volume(rng, shape)
+        dims = (shape[1], shape[0], 1) if two_d else shape[::-1]
+        k = int(rng.integers(0, 7))
+        seeds = np.stack([rng.integers(-1, d + 1, size=k) for d in dims], 1).astype(np.int32) if k else np.zeros((0, 3), np.int32)
+        if two_d and k:
+            seeds[:, 2] = 0
+        if k > 1:
+            seeds[-1] = seeds[0]
+        T = int(rng.choice([-3, 0, 1, 1, 2, 5, 41, 255, 256, 1000]))
+        want = oracle.grow(img, seeds, T)
+        got = dev_grow(rg, ctx, img, seeds, T)
+        assert (got == want).all(), (block, case, shape, T, seeds.tolist())
